@@ -1,0 +1,116 @@
+/* vq_b200.h -- C ABI of libvq_b200.so: the B200 (sm_100a) vector-quantisation hot path.
+ *
+ * What this boundary replaces.  The reference (nnnagle/vq-vae) is pure in-process Python and its
+ * quantiser source is absent from the tree; there is no reference FFI to mirror.
+ * The entry points below are the device-side halves of the steps the reference's call sites require
+ * of `model.quant` (row labels = SURVEY.md section 8a):
+ *
+ *   a-1  nearest-codebook search        scripts/train_vqvae.py:11,287 ; frl/config/frl_model_v0.yaml:29-33
+ *   a-2  gather q = E[idx]              scripts/export_codebook.py:104 (codebook is [K, D])
+ *   a-3  straight-through output        frl/config/frl_model_v0.yaml:35 ; scripts/train_vqvae.py:433-434
+ *   a-4  commitment / codebook loss     frl/config/frl_bindings_v0.yaml:887-891 ; scripts/train_vqvae.py:189,321,328
+ *   a-5  per-code counts and sums       scripts/train_vqvae.py:191-194,433-436 ; scripts/config.yaml:61
+ *   a-7  EMA codebook update            scripts/train_vqvae.py:435-436 (ema_decay 0.99, ema_eps 1e-5)
+ *   a-8  usage / dead-code accounting   scripts/train_vqvae.py:92,197-198 ; scripts/export_codebook.py:124-128
+ *   a-9  perplexity                     scripts/train_vqvae.py:32,287,357
+ *
+ * Conventions.  Every pointer is a DEVICE pointer owned by the caller (torch tensors, kept alive until the
+ * stream has drained) unless it says "host".  Every function enqueues work on `stream` and returns without
+ * synchronising.  Return value 0 = ok; otherwise one of VQ_ERR_* and vq_last_error() holds a message
+ * (thread-local).  No torch / ATen types appear here; the Python side binds these with ctypes
+ * (vq-vae_b200/_lib.py) -- see INTEGRATION.md.  There is no CPU fallback behind any of these.
+ */
+#ifndef VQ_B200_H_
+#define VQ_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef VQ_STREAM_T_DEFINED
+#define VQ_STREAM_T_DEFINED
+typedef struct CUstream_st* vq_stream_t; /* == cudaStream_t */
+#endif
+
+#define VQ_ABI_VERSION 1
+
+enum { VQ_OK = 0, VQ_ERR_ARG = 1, VQ_ERR_CUDA = 2, VQ_ERR_UNSUPPORTED = 3 };
+enum { VQ_DT_BF16 = 0, VQ_DT_F32 = 1 };
+/* arithmetic of the distance search */
+enum {
+    VQ_SEARCH_BF16 = 0, /* z, E rounded to bf16, fp32 accumulate: tcgen05 tensor-core kernel            */
+    VQ_SEARCH_F32 = 1   /* fp32 FMA on the CUDA cores, the 1e-5 tier                                     */
+};
+/* what vq_gather_st_loss_scatter accumulates per code */
+enum {
+    VQ_STAT_SUM_Z = 0,  /* sum_k = sum z_n         (EMA statistics, a-5)                                 */
+    VQ_STAT_SUM_RESID = 1 /* sum_k = sum (z_n - e_k) (st mode: codebook gradient = -2g/(ND) * sum_k)     */
+};
+
+int vq_abi_version(void);
+const char* vq_last_error(void);
+
+/* Number of floats the e_norm2 array must hold: K rounded up to the search kernel's code tile (padding = +inf). */
+int vq_norm_elems(int K);
+
+/* Scratch bytes for one step at these sizes (covers vq_assign and vq_gather_st_loss_scatter). */
+int vq_workspace_bytes(int64_t N, int K, int D, int in_dtype, size_t* out_bytes /* host */);
+
+/* a-7 tail: refresh what the search reads.  E_bf16 [K, D] bf16 shadow (may be NULL for VQ_SEARCH_F32);
+ * e_norm2 [vq_norm_elems(K)] fp32 = ||e_k||^2 of the bf16-rounded rows (VQ_SEARCH_BF16) or of the fp32
+ * rows (VQ_SEARCH_F32); padding entries are +inf. */
+int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf16, float* e_norm2,
+                        vq_stream_t stream);
+
+/* a-1: idx[n] = argmin_k ( ||e_k||^2 - 2 z_n.e_k ), lowest index wins ties.  z is [N, D] with row stride
+ * ldz elements.  smin (nullable) receives the minimal score (add ||z_n||^2 for the squared distance).
+ * Rows containing non-finite values get an unspecified in-range index here; vq_gather_st_loss_scatter
+ * canonicalises them to 0. */
+int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32, const void* E_bf16,
+              const float* e_norm2, int K, int search, int32_t* idx, float* smin /* nullable */, void* ws,
+              vq_stream_t stream);
+
+/* a-2..a-5 in ONE pass over z: q_out[n] = E_f32[idx[n]] (cast to out_dtype == in_dtype), sq_err_sum[0] =
+ * sum (z - q)^2 (fp32, over finite rows), and -- when code_cnt/code_sum are non-NULL -- cnt_k and the per-code
+ * sums selected by stat_kind.  Rows are visited in code-sorted order (a counting sort of idx built in ws),
+ * so the sums are segmented reductions in registers with one vector red per (code, 64-row slice).
+ * deterministic != 0 makes the visiting order, hence every fp32 sum, run-to-run reproducible.
+ * idx is in/out: rows with non-finite z are rewritten to 0, get q = E[0] and are left out of all sums. */
+int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx,
+                              const float* E_f32, int K, void* q_out, int out_dtype, int64_t ldq, float* sq_err_sum,
+                              float* code_cnt /* [K] or NULL */, float* code_sum /* [K*D] or NULL */, int stat_kind,
+                              int deterministic, void* ws, vq_stream_t stream);
+
+/* a-7..a-9 (after the cross-GPU reduce of code_cnt/code_sum, a-6):
+ *   n_k <- g n_k + (1-g) cnt_k ; m_k <- g m_k + (1-g) sum_k ; n^_k = (n_k+eps)/(sum n + K eps) * sum n ;
+ *   e_k <- m_k / n^_k ; then the search shadow (E_bf16, e_norm2) is refreshed in the same launch.
+ * do_ema == 0 skips the codebook update (st mode) but still does usage / dead / perplexity:
+ *   usage_total += cnt ; steps_since_used = cnt>0 ? 0 : +1 ; n_dead = #{steps_since_used >= dead_after} ;
+ *   perplexity = exp(-sum p log(p + 1e-10)), p = cnt / sum cnt. */
+int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* code_cnt, const float* code_sum, int K,
+                  int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
+                  int64_t* usage_total, int32_t* steps_since_used, float* perplexity /* [1] */,
+                  int32_t* n_dead /* [1] */, int dead_after, int update_usage, void* ws, vq_stream_t stream);
+
+/* a-3/a-4 backward: grad_z = grad_q + (*grad_loss) * coef * (z - q), coef = 2*beta/(N*D) passed by the host.
+ * grad_q may be NULL (no gradient arrived through the quantised output). */
+int vq_backward(const void* z, const void* q, const void* grad_q /* nullable */, int64_t N, int D, int64_t ldz,
+                const float* grad_loss /* device [1] */, float coef, void* grad_z, int dtype, vq_stream_t stream);
+
+/* st mode: grad_E[k] = -(*grad_loss) * coef * resid_sum[k]  (resid_sum from VQ_STAT_SUM_RESID, coef = 2/(N*D)). */
+int vq_codebook_grad(const float* resid_sum, int K, int D, const float* grad_loss /* device [1] */, float coef,
+                     float* grad_E, vq_stream_t stream);
+
+/* fp32 -> bf16 row cast used when fp32 latents go through VQ_SEARCH_BF16 (dst is [N, D] dense). */
+int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_stream_t stream);
+
+/* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
+int64_t vq_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VQ_B200_H_ */

@@ -1,0 +1,148 @@
+// extern "C" surface of libvq_b200.so (declared in include/vq_b200.h).  Argument checking, workspace carve-up
+// and dispatch only; the kernels live in vq_assign_tc.cu / vq_assign_simt.cu / vq_pass.cu / vq_ema.cu.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "vq_common.cuh"
+
+namespace vq {
+
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int sm_count() {
+    static int cached_dev = -1, cached = 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached = n;
+        cached_dev = dev;
+    }
+    return cached;
+}
+
+int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* code_cnt, const float* code_sum,
+                      int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
+                      int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
+                      int dead_after, int update_usage, void* ws, cudaStream_t st);
+int launch_backward(const void* z, const void* q, const void* gq, int64_t N, int D, int64_t ldz,
+                    const float* grad_loss, float coef, void* gz, int dtype, cudaStream_t st);
+int launch_codebook_grad(const float* resid, int K, int D, const float* grad_loss, float coef, float* gE,
+                         cudaStream_t st);
+
+}  // namespace vq
+
+using namespace vq;
+
+extern "C" {
+
+int vq_abi_version(void) { return VQ_ABI_VERSION; }
+const char* vq_last_error(void) { return g_err; }
+int64_t vq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int vq_norm_elems(int K) { return K <= 0 ? 0 : round_up(K, 256); }
+
+int vq_workspace_bytes(int64_t N, int K, int D, int in_dtype, size_t* out_bytes) {
+    VQ_REQUIRE(out_bytes != nullptr, "vq_workspace_bytes: out_bytes is NULL");
+    VQ_REQUIRE(N >= 0 && K > 0 && D > 0 && (in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32),
+               "vq_workspace_bytes: bad arguments N=%lld K=%d D=%d in_dtype=%d", (long long)N, K, D, in_dtype);
+    *out_bytes = ws_layout(N, K, D, in_dtype).total;
+    return VQ_OK;
+}
+
+int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf16, float* e_norm2,
+                        vq_stream_t stream) {
+    VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_prepare_codebook: bad search mode %d", search);
+    VQ_REQUIRE(search != VQ_SEARCH_BF16 || E_bf16 != nullptr, "vq_prepare_codebook: E_bf16 required for VQ_SEARCH_BF16");
+    return launch_ema_update(const_cast<float*>(E_f32), nullptr, nullptr, nullptr, nullptr, K, D, 0.f, 0.f, 0, search,
+                             E_bf16, e_norm2, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, stream);
+}
+
+int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32, const void* E_bf16,
+              const float* e_norm2, int K, int search, int32_t* idx, float* smin, void* ws, vq_stream_t stream) {
+    VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_assign: bad in_dtype %d", in_dtype);
+    VQ_REQUIRE(N >= 0 && D > 0 && K > 0 && ldz >= D, "vq_assign: bad shape N=%lld D=%d K=%d ldz=%lld", (long long)N, D,
+               K, (long long)ldz);
+    VQ_REQUIRE(idx != nullptr && e_norm2 != nullptr, "vq_assign: idx and e_norm2 are required");
+    if (N == 0) return VQ_OK;
+    VQ_REQUIRE(z != nullptr, "vq_assign: z is NULL");
+    if (search == VQ_SEARCH_F32) {
+        VQ_REQUIRE(E_f32 != nullptr, "vq_assign: E_f32 required for VQ_SEARCH_F32");
+        return launch_assign_simt(z, in_dtype, N, D, ldz, E_f32, e_norm2, K, idx, smin, stream);
+    }
+    VQ_REQUIRE(search == VQ_SEARCH_BF16, "vq_assign: bad search mode %d", search);
+    VQ_REQUIRE(E_bf16 != nullptr, "vq_assign: E_bf16 required for VQ_SEARCH_BF16");
+    const void* zb = z;
+    int64_t ldb = ldz;
+    if (in_dtype == VQ_DT_F32) {
+        VQ_REQUIRE(ws != nullptr, "vq_assign: workspace required to stage fp32 latents as bf16");
+        void* stage = static_cast<uint8_t*>(ws) + ws_layout(N, K, D, in_dtype).zbf16;
+        int rc = launch_cast_bf16(static_cast<const float*>(z), N, D, ldz, stage, stream);
+        if (rc != VQ_OK) return rc;
+        zb = stage;
+        ldb = D;
+    }
+    if (!assign_tc_supported(N, D, ldb, K)) {
+        set_error("vq_assign(VQ_SEARCH_BF16): shape N=%lld D=%d ld=%lld K=%d not supported by the tensor-core kernel "
+                  "(needs D %% 8 == 0, 8 <= D <= 512, ld %% 8 == 0); use VQ_SEARCH_F32",
+                  (long long)N, D, (long long)ldb, K);
+        return VQ_ERR_UNSUPPORTED;
+    }
+    return launch_assign_tc(zb, N, D, ldb, E_bf16, e_norm2, K, idx, smin, stream);
+}
+
+int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx,
+                              const float* E_f32, int K, void* q_out, int out_dtype, int64_t ldq, float* sq_err_sum,
+                              float* code_cnt, float* code_sum, int stat_kind, int deterministic, void* ws,
+                              vq_stream_t stream) {
+    VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_gather_st_loss_scatter: bad in_dtype %d", in_dtype);
+    VQ_REQUIRE(out_dtype == in_dtype, "vq_gather_st_loss_scatter: out_dtype must equal in_dtype");
+    VQ_REQUIRE(stat_kind == VQ_STAT_SUM_Z || stat_kind == VQ_STAT_SUM_RESID, "bad stat_kind %d", stat_kind);
+    VQ_REQUIRE(idx != nullptr && E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (z != nullptr && q_out != nullptr)),
+               "vq_gather_st_loss_scatter: NULL argument");
+    return launch_gather_pass(z, in_dtype, N, D, ldz, idx, E_f32, K, q_out, ldq, sq_err_sum, code_cnt, code_sum,
+                              stat_kind, deterministic, ws, stream);
+}
+
+int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* code_cnt, const float* code_sum, int K,
+                  int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
+                  int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead, int dead_after,
+                  int update_usage, void* ws, vq_stream_t stream) {
+    VQ_REQUIRE(code_cnt != nullptr, "vq_ema_update: code_cnt is NULL");
+    VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_ema_update: bad search mode %d", search);
+    return launch_ema_update(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, do_ema, search, E_bf16,
+                             e_norm2, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws,
+                             stream);
+}
+
+int vq_backward(const void* z, const void* q, const void* grad_q, int64_t N, int D, int64_t ldz,
+                const float* grad_loss, float coef, void* grad_z, int dtype, vq_stream_t stream) {
+    VQ_REQUIRE(dtype == VQ_DT_BF16 || dtype == VQ_DT_F32, "vq_backward: bad dtype %d", dtype);
+    VQ_REQUIRE(N == 0 || (z != nullptr && q != nullptr && grad_z != nullptr && grad_loss != nullptr),
+               "vq_backward: NULL argument");
+    return launch_backward(z, q, grad_q, N, D, ldz, grad_loss, coef, grad_z, dtype, stream);
+}
+
+int vq_codebook_grad(const float* resid_sum, int K, int D, const float* grad_loss, float coef, float* grad_E,
+                     vq_stream_t stream) {
+    VQ_REQUIRE(resid_sum != nullptr && grad_loss != nullptr && grad_E != nullptr, "vq_codebook_grad: NULL argument");
+    return launch_codebook_grad(resid_sum, K, D, grad_loss, coef, grad_E, stream);
+}
+
+int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_stream_t stream) {
+    VQ_REQUIRE(N == 0 || (src != nullptr && dst != nullptr), "vq_cast_bf16: NULL argument");
+    return launch_cast_bf16(src, N, D, ld, dst, stream);
+}
+
+}  // extern "C"

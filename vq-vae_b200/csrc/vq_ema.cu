@@ -1,0 +1,212 @@
+// a-7 .. a-9  EMA codebook update, usage / dead-code accounting, perplexity; plus the search-shadow refresh
+// (bf16 copy + ||e||^2) and the two small backward kernels (a-3 / a-4).
+// K*D elementwise work (2 M elements at K=8192, D=256): launch-latency bound, reported in microseconds.
+// Required by: scripts/train_vqvae.py:191-194,433-436 (quantizer="ema", ema_decay, ema_eps);
+// scripts/train_vqvae.py:92,197-198 and scripts/export_codebook.py:124-128 (usage); scripts/train_vqvae.py:357
+// (perplexity).  Definitions: SURVEY.md 8(a-7 .. a-9).
+#include <math_constants.h>
+
+#include "vq_common.cuh"
+
+namespace vq {
+namespace {
+
+struct Scal {          // lives at offset 0 of the workspace
+    float tot_new;     // sum_k n_k after the decay step
+    float pad[3];
+};
+
+// one block.  tot_new = sum_k (g n_k + (1-g) cnt_k) in a fixed order (double); usage / dead / perplexity.
+__global__ void __launch_bounds__(1024)
+ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ code_cnt, int K, float decay,
+                  int do_ema, Scal* __restrict__ scal, int64_t* __restrict__ usage_total,
+                  int32_t* __restrict__ steps_since_used, float* __restrict__ perplexity, int32_t* __restrict__ n_dead,
+                  int dead_after, int update_usage) {
+    __shared__ double sh[3][32];
+    const int t = threadIdx.x;
+    const float omg = 1.0f - decay;
+    double s_n = 0.0, s_c = 0.0;
+    int dead = 0;
+    for (int k = t; k < K; k += 1024) {
+        const float c = code_cnt[k];
+        if (do_ema) s_n += (double)__fadd_rn(__fmul_rn(decay, ema_cnt[k]), __fmul_rn(omg, c));
+        s_c += (double)c;
+        if (update_usage) {
+            usage_total[k] += (int64_t)llrintf(c);
+            const int s = c > 0.f ? 0 : steps_since_used[k] + 1;
+            steps_since_used[k] = s;
+            dead += s >= dead_after;
+        } else {
+            dead += steps_since_used[k] >= dead_after;
+        }
+    }
+    double v[3] = {s_n, s_c, (double)dead};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+        if ((t & 31) == 0) sh[i][t >> 5] = v[i];
+    }
+    __syncthreads();
+    if (t < 32) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            v[i] = sh[i][t];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+        }
+        if (t == 0) {
+            scal->tot_new = (float)v[0];
+            n_dead[0] = (int32_t)v[2];
+            sh[1][0] = v[1];
+        }
+    }
+    __syncthreads();
+    const double tot_c = sh[1][0];
+    __syncthreads();
+    // perplexity = exp(-sum p log(p + 1e-10))
+    double h = 0.0;
+    if (tot_c > 0.0)
+        for (int k = t; k < K; k += 1024) {
+            const double p = (double)code_cnt[k] / tot_c;
+            h += p * log(p + 1e-10);
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
+    if ((t & 31) == 0) sh[0][t >> 5] = h;
+    __syncthreads();
+    if (t < 32) {
+        h = sh[0][t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
+        if (t == 0) perplexity[0] = tot_c > 0.0 ? (float)exp(-h) : 1.0f;
+    }
+}
+
+// one warp per code row.  do_ema: decay step + Laplace-normalised codebook row; always: refresh bf16 shadow + norm.
+__global__ void __launch_bounds__(256)
+ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __restrict__ ema_sum,
+                 const float* __restrict__ code_cnt, const float* __restrict__ code_sum, int K, int D, float decay,
+                 float eps, float k_eps, int do_ema, int search, const Scal* __restrict__ scal,
+                 __nv_bfloat16* __restrict__ E_bf16, float* __restrict__ e_norm2, int norm_elems) {
+    const int lane = threadIdx.x & 31;
+    const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (k >= norm_elems) return;
+    if (k >= K) {
+        if (lane == 0) e_norm2[k] = CUDART_INF_F;
+        return;
+    }
+    const float omg = 1.0f - decay;
+    float nhat = 1.f;
+    if (do_ema) {
+        const float n = __fadd_rn(__fmul_rn(decay, ema_cnt[k]), __fmul_rn(omg, code_cnt[k]));
+        const float tot = scal->tot_new;
+        nhat = __fmul_rn(__fdiv_rn(__fadd_rn(n, eps), __fadd_rn(tot, k_eps)), tot);
+        __syncwarp();
+        if (lane == 0) ema_cnt[k] = n;
+    }
+    float nrm = 0.f;
+    for (int d = lane; d < D; d += 32) {
+        const int64_t o = (int64_t)k * D + d;
+        float ev;
+        if (do_ema) {
+            const float m = __fadd_rn(__fmul_rn(decay, ema_sum[o]), __fmul_rn(omg, code_sum[o]));
+            ema_sum[o] = m;
+            ev = __fdiv_rn(m, nhat);
+            E[o] = ev;
+        } else {
+            ev = E[o];
+        }
+        const __nv_bfloat16 eb = __float2bfloat16_rn(ev);
+        if (E_bf16 != nullptr) E_bf16[o] = eb;
+        const float en = search == VQ_SEARCH_BF16 ? __bfloat162float(eb) : ev;
+        nrm = fmaf(en, en, nrm);
+    }
+    nrm = warp_sum(nrm);
+    if (lane == 0) e_norm2[k] = nrm;
+}
+
+template <typename T>
+__global__ void backward_kernel(const T* __restrict__ z, const T* __restrict__ q, const T* __restrict__ gq, int64_t N,
+                                int D, int64_t ldz, const float* __restrict__ grad_loss, float coef,
+                                T* __restrict__ gz) {
+    const float c = coef * grad_loss[0];
+    const int64_t total = N * (int64_t)D;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / D;
+        const int d = (int)(i - r * D);
+        const float zf = (float)z[r * ldz + d];
+        const float qf = (float)q[i];
+        float g = c * (zf - qf);
+        if (gq != nullptr) g += (float)gq[i];
+        gz[i] = (T)g;
+    }
+}
+
+__global__ void codebook_grad_kernel(const float* __restrict__ resid, int64_t n, const float* __restrict__ grad_loss,
+                                     float coef, float* __restrict__ gE) {
+    const float c = -coef * grad_loss[0];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        gE[i] = c * resid[i];
+}
+
+}  // namespace
+
+int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* code_cnt, const float* code_sum,
+                      int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
+                      int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
+                      int dead_after, int update_usage, void* ws, cudaStream_t st) {
+    VQ_REQUIRE(K > 0 && D > 0, "vq_ema_update: bad shape K=%d D=%d", K, D);
+    VQ_REQUIRE(E_f32 != nullptr && e_norm2 != nullptr, "vq_ema_update: E_f32 and e_norm2 are required");
+    Scal* scal = static_cast<Scal*>(ws);
+    if (code_cnt != nullptr) {
+        VQ_REQUIRE(ws != nullptr && usage_total != nullptr && steps_since_used != nullptr && perplexity != nullptr &&
+                       n_dead != nullptr,
+                   "vq_ema_update: statistics buffers and workspace are required when code_cnt is given");
+        VQ_REQUIRE(!do_ema || (ema_cnt != nullptr && ema_sum != nullptr && code_sum != nullptr),
+                   "vq_ema_update: do_ema needs ema_cnt, ema_sum and code_sum");
+        ema_totals_kernel<<<1, 1024, 0, st>>>(ema_cnt, code_cnt, K, decay, do_ema, scal, usage_total, steps_since_used,
+                                              perplexity, n_dead, dead_after, update_usage);
+        VQ_CHECK_CUDA(cudaGetLastError());
+        count_launch();
+    } else {
+        VQ_REQUIRE(!do_ema, "vq_ema_update: do_ema without code_cnt");
+    }
+    const int ne = vq_norm_elems(K);
+    const float k_eps = (float)((double)K * (double)eps);
+    ema_apply_kernel<<<(ne + 7) / 8, 256, 0, st>>>(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, k_eps,
+                                                   do_ema, search, scal, static_cast<__nv_bfloat16*>(E_bf16), e_norm2,
+                                                   ne);
+    VQ_CHECK_CUDA(cudaGetLastError());
+    count_launch();
+    return VQ_OK;
+}
+
+int launch_backward(const void* z, const void* q, const void* gq, int64_t N, int D, int64_t ldz,
+                    const float* grad_loss, float coef, void* gz, int dtype, cudaStream_t st) {
+    VQ_REQUIRE(N >= 0 && D > 0 && ldz >= D, "vq_backward: bad shape");
+    if (N == 0) return VQ_OK;
+    const int blocks = sm_count() * 8;
+    if (dtype == VQ_DT_F32)
+        backward_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(z), static_cast<const float*>(q),
+                                                       static_cast<const float*>(gq), N, D, ldz, grad_loss, coef,
+                                                       static_cast<float*>(gz));
+    else
+        backward_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
+            static_cast<const __nv_bfloat16*>(z), static_cast<const __nv_bfloat16*>(q),
+            static_cast<const __nv_bfloat16*>(gq), N, D, ldz, grad_loss, coef, static_cast<__nv_bfloat16*>(gz));
+    VQ_CHECK_CUDA(cudaGetLastError());
+    count_launch();
+    return VQ_OK;
+}
+
+int launch_codebook_grad(const float* resid, int K, int D, const float* grad_loss, float coef, float* gE,
+                         cudaStream_t st) {
+    VQ_REQUIRE(K > 0 && D > 0, "vq_codebook_grad: bad shape");
+    codebook_grad_kernel<<<sm_count() * 4, 256, 0, st>>>(resid, (int64_t)K * D, grad_loss, coef, gE);
+    VQ_CHECK_CUDA(cudaGetLastError());
+    count_launch();
+    return VQ_OK;
+}
+
+}  // namespace vq

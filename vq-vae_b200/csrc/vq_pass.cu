@@ -1,0 +1,509 @@
+// a-2 .. a-5  One pass over z: codebook gather, straight-through output, squared-error reduction and the
+// per-code counts / sums for the EMA update (or, in st mode, the residual sums the codebook gradient needs).
+//
+// HBM-bound: algorithmic traffic is D*s (read z) + 4 (idx) + D*s (write q) bytes per latent vector; the fp32
+// master codebook (K*D*4 <= 8 MiB at K=8192, D=256) stays L2-resident.  To keep the scatter-add off the L2
+// atomic units, rows are visited in CODE-SORTED order: a counting sort of idx (histogram -> exclusive scan ->
+// slot claim; 3 tiny kernels touching 4 bytes per row) yields `perm`, and every lane group then walks 64
+// consecutive sorted positions, keeping the running per-code sum in registers and issuing one vector `red`
+// per (code, 64-row slice) -- about K + N/64 reds of D floats per step instead of N.
+// Required by: scripts/export_codebook.py:104 (gather from [K, D]); frl/config/frl_model_v0.yaml:35 (straight
+// through); frl/config/frl_bindings_v0.yaml:887-891 (commitment + codebook terms); scripts/train_vqvae.py:433-436
+// (EMA statistics).  Definitions: SURVEY.md 8(a-2 .. a-5).
+#include "vq_common.cuh"
+
+namespace vq {
+namespace {
+
+constexpr int LG = 64;   // sorted positions walked by one lane group
+
+__device__ __forceinline__ unsigned lanemask_lt() {
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// ------------------------------------------------------------------------------ counting sort of idx
+__global__ void hist_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int* __restrict__ cnt,
+                            int* __restrict__ chunk_cnt, int rows_per_chunk) {
+    const int lane = threadIdx.x & 31;
+    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (int64_t)gridDim.x * blockDim.x) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        if (chunk_cnt != nullptr) {                  // deterministic mode: per-chunk histograms as well
+            atomicAdd(&chunk_cnt[(n / rows_per_chunk) * K + c], 1);
+        }
+        const unsigned m = __match_any_sync(__activemask(), c);
+        if (lane == __ffs(m) - 1) atomicAdd(&cnt[c], __popc(m));
+    }
+}
+
+// one block; exclusive scan of cnt[0..K) -> start[0..K], cursor[k] = start[k]
+__global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ cnt, int K, int* __restrict__ start,
+                                                    int* __restrict__ cursor) {
+    __shared__ int warp_tot[32];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int per = (K + 1023) / 1024;
+    const int a = t * per, b = min(K, a + per);
+    int s = 0;
+    for (int k = a; k < b; ++k) s += cnt[k];
+    int inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) warp_tot[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int v = warp_tot[lane], iv = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, iv, o);
+            if (lane >= o) iv += u;
+        }
+        warp_tot[lane] = iv - v;
+    }
+    __syncthreads();
+    int run = warp_tot[w] + inc - s;
+    for (int k = a; k < b; ++k) {
+        start[k] = run;
+        cursor[k] = run;
+        run += cnt[k];
+    }
+    if (b == K && a < K) start[K] = run;
+    if (K == 0 && t == 0) start[0] = 0;
+}
+
+__global__ void scatter_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int* __restrict__ cursor,
+                               int32_t* __restrict__ perm) {
+    const int lane = threadIdx.x & 31;
+    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (int64_t)gridDim.x * blockDim.x) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        const unsigned m = __match_any_sync(__activemask(), c);
+        const int leader = __ffs(m) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&cursor[c], __popc(m));
+        base = __shfl_sync(m, base, leader);
+        perm[base + __popc(m & lanemask_lt())] = (int32_t)n;
+    }
+}
+
+// deterministic slot claim.  chunk_cnt[b][k] holds the number of rows of chunk b with code k; turn every column
+// into its running offset (start[k] + rows of code k in earlier chunks) ...
+__global__ void chunk_offsets_kernel(int* __restrict__ chunk_cnt, int nchunks, int K, const int* __restrict__ start) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    int run = start[k];
+    for (int b = 0; b < nchunks; ++b) {
+        const int t = chunk_cnt[(int64_t)b * K + k];
+        chunk_cnt[(int64_t)b * K + k] = run;
+        run += t;
+    }
+}
+// ... then one warp per chunk walks its rows in order, 32 at a time, so that equal codes keep row order.
+__global__ void scatter_stable_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int* __restrict__ chunk_off,
+                                      int rows_per_chunk, int nchunks, int32_t* __restrict__ perm) {
+    const int lane = threadIdx.x & 31;
+    const int chunk = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (chunk >= nchunks) return;
+    const int64_t a = (int64_t)chunk * rows_per_chunk;
+    const int64_t b = min(N, a + rows_per_chunk);
+    volatile int* off = chunk_off + (int64_t)chunk * K;
+    for (int64_t n0 = a; n0 < b; n0 += 32) {
+        const int64_t n = n0 + lane;
+        const bool valid = n < b;
+        int c = valid ? idx[n] : -1 - lane;           // distinct dummies never match a real code
+        if (valid && (unsigned)c >= (unsigned)K) c = 0;
+        const unsigned m = __match_any_sync(0xffffffffu, c);
+        const int leader = __ffs(m) - 1;
+        int base = 0;
+        if (valid && lane == leader) {
+            base = off[c];
+            off[c] = base + __popc(m);
+        }
+        __syncwarp();
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (valid) perm[base + __popc(m & lanemask_lt())] = (int32_t)n;
+    }
+}
+
+// ------------------------------------------------------------------------------ the fused pass
+template <typename T> struct VecIO;
+template <> struct VecIO<__nv_bfloat16> {
+    static constexpr int EPV = 8;
+    __device__ static __forceinline__ void unpack(const int4& v, float (&f)[8]) {
+        f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+        f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+    }
+    __device__ static __forceinline__ int4 pack(const float (&f)[8]) {
+        return make_int4((int)pack_bf16(f[0], f[1]), (int)pack_bf16(f[2], f[3]), (int)pack_bf16(f[4], f[5]),
+                         (int)pack_bf16(f[6], f[7]));
+    }
+    __device__ static __forceinline__ bool nonfinite(const int4& v) {   // any bf16 with an all-ones exponent
+        const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+        bool bad = false;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            bad |= ((w[i] & 0x7f800000u) == 0x7f800000u) | ((w[i] & 0x00007f80u) == 0x00007f80u);
+        return bad;
+    }
+};
+template <> struct VecIO<float> {
+    static constexpr int EPV = 4;
+    __device__ static __forceinline__ void unpack(const int4& v, float (&f)[4]) {
+        f[0] = __int_as_float(v.x); f[1] = __int_as_float(v.y); f[2] = __int_as_float(v.z); f[3] = __int_as_float(v.w);
+    }
+    __device__ static __forceinline__ int4 pack(const float (&f)[4]) {
+        return make_int4(__float_as_int(f[0]), __float_as_int(f[1]), __float_as_int(f[2]), __float_as_int(f[3]));
+    }
+    __device__ static __forceinline__ bool nonfinite(const int4& v) {
+        const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+        bool bad = false;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) bad |= (w[i] & 0x7f800000u) == 0x7f800000u;
+        return bad;
+    }
+};
+
+// T: storage type of z and q.  LPR lanes cooperate on one row (16 bytes per lane per vector), VPL vectors per lane.
+// perm == nullptr visits rows in natural order (no statistics wanted: eval mode).
+template <typename T, int VPL, int LPR>
+__global__ void __launch_bounds__(256)
+pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
+            const int32_t* __restrict__ perm, const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
+            float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
+            int stat_kind) {
+    using IO = VecIO<T>;
+    constexpr int EPV = IO::EPV;
+    constexpr int G = 32 / LPR;
+    constexpr int IDS = LG / LPR;
+    constexpr int U = VPL == 1 ? 8 : (VPL == 2 ? 4 : 2);
+    static_assert(LPR % U == 0 || U % LPR == 0, "batching");
+    constexpr int UB = U < LPR ? U : LPR;             // rows fetched per batch
+
+    const int lane = threadIdx.x & 31;
+    const int g = lane / LPR, lg = lane % LPR;
+    const unsigned gmask = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << (g * LPR);
+    const int64_t warp_global = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t p0 = (warp_global * G + g) * LG;
+    const int V = D / EPV;
+
+    int rows[IDS], codes[IDS];
+#pragma unroll
+    for (int i = 0; i < IDS; ++i) {
+        const int64_t pos = p0 + i * LPR + lg;
+        int r = -1, c = -1;
+        if (pos < N) {
+            r = perm != nullptr ? perm[pos] : (int)pos;
+            c = idx[r];
+            if ((unsigned)c >= (unsigned)K) c = 0;
+        }
+        rows[i] = r;
+        codes[i] = c;
+    }
+
+    float e[VPL][EPV], acc[VPL][EPV];
+    int4 qv[VPL];
+#pragma unroll
+    for (int j = 0; j < VPL; ++j) {
+        qv[j] = make_int4(0, 0, 0, 0);
+#pragma unroll
+        for (int x = 0; x < EPV; ++x) { e[j][x] = 0.f; acc[j][x] = 0.f; }
+    }
+    float loss = 0.f;
+    int cnt = 0, cur = -1;
+
+    auto flush = [&]() {
+        if (cur >= 0 && cnt > 0 && code_sum != nullptr) {
+#pragma unroll
+            for (int j = 0; j < VPL; ++j) {
+                const int v = lg + j * LPR;
+                if (v < V) {
+                    float* dst = code_sum + (int64_t)cur * D + v * EPV;
+#pragma unroll
+                    for (int x = 0; x < EPV; x += 4) red_add_v4(dst + x, acc[j][x], acc[j][x + 1], acc[j][x + 2], acc[j][x + 3]);
+                }
+            }
+            if (lg == 0) atomicAdd(code_cnt + cur, (float)cnt);
+        }
+#pragma unroll
+        for (int j = 0; j < VPL; ++j)
+#pragma unroll
+            for (int x = 0; x < EPV; ++x) acc[j][x] = 0.f;
+        cnt = 0;
+    };
+
+#pragma unroll
+    for (int i = 0; i < IDS; ++i) {
+#pragma unroll 1
+        for (int l0 = 0; l0 < LPR; l0 += UB) {
+            int rr[UB], cc[UB];
+            int4 zv[UB][VPL];
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                rr[u] = __shfl_sync(0xffffffffu, rows[i], g * LPR + l0 + u);
+                cc[u] = __shfl_sync(0xffffffffu, codes[i], g * LPR + l0 + u);
+#pragma unroll
+                for (int j = 0; j < VPL; ++j) {
+                    const int v = lg + j * LPR;
+                    zv[u][j] = make_int4(0, 0, 0, 0);
+                    if (rr[u] >= 0 && v < V) zv[u][j] = ld_stream_16(z + (int64_t)rr[u] * ldz + v * EPV);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const bool valid = rr[u] >= 0;
+                bool nf = false;
+#pragma unroll
+                for (int j = 0; j < VPL; ++j) nf |= IO::nonfinite(zv[u][j]);
+                const bool bad = (__ballot_sync(0xffffffffu, valid && nf) & gmask) != 0;
+                if (valid) {
+                    if (cc[u] != cur) {
+                        flush();
+                        cur = cc[u];
+#pragma unroll
+                        for (int j = 0; j < VPL; ++j) {
+                            const int v = lg + j * LPR;
+                            if (v < V) {
+                                const float4* src = reinterpret_cast<const float4*>(E + (int64_t)cur * D + v * EPV);
+#pragma unroll
+                                for (int x = 0; x < EPV; x += 4) {
+                                    const float4 t = __ldg(src + x / 4);
+                                    e[j][x] = t.x; e[j][x + 1] = t.y; e[j][x + 2] = t.z; e[j][x + 3] = t.w;
+                                }
+                                qv[j] = IO::pack(e[j]);
+                            }
+                        }
+                    }
+                    if (!bad) {
+#pragma unroll
+                        for (int j = 0; j < VPL; ++j) {
+                            const int v = lg + j * LPR;
+                            if (v < V) {
+                                float zf[EPV];
+                                IO::unpack(zv[u][j], zf);
+#pragma unroll
+                                for (int x = 0; x < EPV; ++x) {
+                                    const float d = zf[x] - e[j][x];
+                                    loss = fmaf(d, d, loss);
+                                    acc[j][x] += stat_kind == VQ_STAT_SUM_RESID ? d : zf[x];
+                                }
+                                st_stream_16(q + (int64_t)rr[u] * ldq + v * EPV, qv[j]);
+                            }
+                        }
+                        ++cnt;
+                    } else {
+                        // non-finite latent row: idx := 0, q := E[0], no contribution to loss or statistics
+#pragma unroll
+                        for (int j = 0; j < VPL; ++j) {
+                            const int v = lg + j * LPR;
+                            if (v < V) {
+                                float e0[EPV];
+#pragma unroll
+                                for (int x = 0; x < EPV; ++x) e0[x] = __ldg(E + v * EPV + x);
+                                st_stream_16(q + (int64_t)rr[u] * ldq + v * EPV, IO::pack(e0));
+                            }
+                        }
+                        if (lg == 0) idx[rr[u]] = 0;
+                    }
+                }
+            }
+        }
+    }
+    flush();
+    loss = warp_sum(loss);
+    if (lane == 0) loss_partial[warp_global] = loss;
+}
+
+// any D / alignment: one warp per row, scalar accesses, plain atomics.  Correct but slow; only odd shapes land here.
+template <typename T>
+__global__ void __launch_bounds__(256)
+pass_generic_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
+                    const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
+                    float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
+                    int stat_kind) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    float loss = 0.f;
+    if (row < N) {
+        int c = idx[row];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        bool nf = false;
+        for (int d = lane; d < D; d += 32) {
+            const float v = (float)z[row * ldz + d];
+            nf |= !isfinite(v);
+        }
+        const bool bad = __any_sync(0xffffffffu, nf);
+        if (bad) {
+            c = 0;
+            if (lane == 0) idx[row] = 0;
+        }
+        for (int d = lane; d < D; d += 32) {
+            const float ev = E[(int64_t)c * D + d];
+            q[row * ldq + d] = (T)ev;
+            if (!bad) {
+                const float zf = (float)z[row * ldz + d];
+                const float df = zf - ev;
+                loss = fmaf(df, df, loss);
+                if (code_sum != nullptr) atomicAdd(code_sum + (int64_t)c * D + d, stat_kind == VQ_STAT_SUM_RESID ? df : zf);
+            }
+        }
+        if (!bad && lane == 0 && code_cnt != nullptr) atomicAdd(code_cnt + c, 1.f);
+    }
+    loss = warp_sum(loss);
+    if (lane == 0) loss_partial[row < N ? row : N] = loss;   // slot N is a discard slot
+}
+
+// fixed-order reduction of the per-warp partial sums (double accumulate) -> out[0]
+__global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ part, int64_t n,
+                                                               float* __restrict__ out) {
+    __shared__ double sh[32];
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += 1024) s += (double)part[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        s = sh[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (threadIdx.x == 0) out[0] = (float)s;
+    }
+}
+
+template <typename T, int VPL, int LPR>
+int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm, const float* E,
+                  int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt, float* code_sum,
+                  int stat_kind, cudaStream_t st) {
+    constexpr int G = 32 / LPR;
+    const int64_t groups = ceil_div64(N, LG);
+    const int64_t warps = ceil_div64(groups, G);
+    const int64_t blocks = ceil_div64(warps, 8);
+    *nparts = blocks * 8;
+    pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
+                                                              static_cast<T*>(q), ldq, part, code_cnt, code_sum,
+                                                              stat_kind);
+    return VQ_OK;
+}
+
+template <typename T>
+int launch_pass_dispatch(int V, const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm,
+                         const float* E, int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt,
+                         float* code_sum, int stat_kind, cudaStream_t st) {
+#define VQ_PASS(VPL, LPR) \
+    return launch_pass_t<T, VPL, LPR>(z, N, D, ldz, idx, perm, E, K, q, ldq, part, nparts, code_cnt, code_sum, stat_kind, st)
+    if (V <= 4) VQ_PASS(1, 4);
+    if (V <= 8) VQ_PASS(1, 8);
+    if (V <= 16) VQ_PASS(1, 16);
+    if (V <= 32) VQ_PASS(1, 32);
+    if (V <= 64) VQ_PASS(2, 32);
+    VQ_PASS(4, 32);
+#undef VQ_PASS
+}
+
+}  // namespace
+
+// Workspace carve-up shared by vq_workspace_bytes and the launchers.
+WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
+    auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
+    WsLayout L;
+    size_t o = 0;
+    L.scal = o;      o += 256;
+    L.zbf16 = o;     o += in_dtype == VQ_DT_F32 ? al((size_t)N * D * 2) : 0;
+    L.cnt = o;       o += al((size_t)K * 4);
+    L.start = o;     o += al((size_t)(K + 1) * 4);
+    L.cursor = o;    o += al((size_t)K * 4);
+    L.perm = o;      o += al((size_t)N * 4);
+    L.partial = o;   o += al((size_t)(N + 64) * 4);       // generic kernel: one slot per row (+ discard slot)
+    L.rows_per_chunk = (int)((ceil_div64(N, 256) + 31) / 32 * 32);
+    if (L.rows_per_chunk < 1024) L.rows_per_chunk = 1024;
+    L.nchunks = (int)ceil_div64(N, L.rows_per_chunk);
+    L.chunk_cnt = o; o += al((size_t)L.nchunks * K * 4);
+    L.total = o;
+    return L;
+}
+
+int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx, const float* E_f32,
+                       int K, void* q_out, int64_t ldq, float* sq_err_sum, float* code_cnt, float* code_sum,
+                       int stat_kind, int deterministic, void* ws, cudaStream_t st) {
+    VQ_REQUIRE(N >= 0 && N < (int64_t(1) << 31) && D > 0 && K > 0 && ldz >= D && ldq >= D,
+               "vq_gather_st_loss_scatter: bad shape N=%lld D=%d K=%d", (long long)N, D, K);
+    VQ_REQUIRE((code_cnt == nullptr) == (code_sum == nullptr), "code_cnt and code_sum must both be given or both NULL");
+    const bool stats = code_cnt != nullptr;
+    if (stats) {
+        VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
+        VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
+    }
+    if (N == 0) {
+        VQ_CHECK_CUDA(cudaMemsetAsync(sq_err_sum, 0, 4, st));
+        return VQ_OK;
+    }
+    VQ_REQUIRE(ws != nullptr, "vq_gather_st_loss_scatter: workspace required");
+    const WsLayout L = ws_layout(N, K, D, in_dtype);
+    uint8_t* w = static_cast<uint8_t*>(ws);
+    int* cnt_i = reinterpret_cast<int*>(w + L.cnt);
+    int* start = reinterpret_cast<int*>(w + L.start);
+    int* cursor = reinterpret_cast<int*>(w + L.cursor);
+    int32_t* perm = reinterpret_cast<int32_t*>(w + L.perm);
+    float* part = reinterpret_cast<float*>(w + L.partial);
+    int* chunk_cnt = reinterpret_cast<int*>(w + L.chunk_cnt);
+
+    const int es = in_dtype == VQ_DT_F32 ? 4 : 2;
+    const int epv = 16 / es;
+    const bool vec_ok = D % epv == 0 && (ldz * es) % 16 == 0 && (ldq * es) % 16 == 0 &&
+                        (reinterpret_cast<uintptr_t>(z) & 15) == 0 && (reinterpret_cast<uintptr_t>(q_out) & 15) == 0 &&
+                        (reinterpret_cast<uintptr_t>(E_f32) & 15) == 0 && D / epv <= 128;
+    int64_t nparts = 0;
+    if (!vec_ok) {
+        const int64_t blocks = ceil_div64(N, 8);
+        nparts = N;
+        if (in_dtype == VQ_DT_F32)
+            pass_generic_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const float*>(z), N, D, ldz, idx,
+                                                                         E_f32, K, static_cast<float*>(q_out), ldq,
+                                                                         part, code_cnt, code_sum, stat_kind);
+        else
+            pass_generic_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(
+                static_cast<const __nv_bfloat16*>(z), N, D, ldz, idx, E_f32, K, static_cast<__nv_bfloat16*>(q_out), ldq,
+                part, code_cnt, code_sum, stat_kind);
+        VQ_CHECK_CUDA(cudaGetLastError());
+        count_launch();
+    } else {
+        const int32_t* perm_arg = nullptr;
+        if (stats) {
+            const int gs = (int)(ceil_div64(N, 256) < sm_count() * 8 ? ceil_div64(N, 256) : sm_count() * 8);
+            VQ_CHECK_CUDA(cudaMemsetAsync(cnt_i, 0, (size_t)K * 4, st));
+            if (deterministic) VQ_CHECK_CUDA(cudaMemsetAsync(chunk_cnt, 0, (size_t)L.nchunks * K * 4, st));
+            hist_kernel<<<gs, 256, 0, st>>>(idx, N, K, cnt_i, deterministic ? chunk_cnt : nullptr, L.rows_per_chunk);
+            scan_kernel<<<1, 1024, 0, st>>>(cnt_i, K, start, cursor);
+            if (deterministic) {
+                chunk_offsets_kernel<<<(K + 255) / 256, 256, 0, st>>>(chunk_cnt, L.nchunks, K, start);
+                scatter_stable_kernel<<<(L.nchunks + 3) / 4, 128, 0, st>>>(idx, N, K, chunk_cnt, L.rows_per_chunk,
+                                                                           L.nchunks, perm);
+                count_launch();
+            } else {
+                scatter_kernel<<<gs, 256, 0, st>>>(idx, N, K, cursor, perm);
+            }
+            VQ_CHECK_CUDA(cudaGetLastError());
+            count_launch(3);
+            perm_arg = perm;
+        }
+        const int V = D / epv;
+        if (in_dtype == VQ_DT_F32)
+            launch_pass_dispatch<float>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts, code_cnt,
+                                        code_sum, stat_kind, st);
+        else
+            launch_pass_dispatch<__nv_bfloat16>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts,
+                                                code_cnt, code_sum, stat_kind, st);
+        VQ_CHECK_CUDA(cudaGetLastError());
+        count_launch();
+    }
+    reduce_partials_kernel<<<1, 1024, 0, st>>>(part, nparts, sq_err_sum);
+    VQ_CHECK_CUDA(cudaGetLastError());
+    count_launch();
+    return VQ_OK;
+}
+
+}  // namespace vq
