@@ -1,0 +1,143 @@
+"""Thin torch-tensor wrappers over the C ABI (include/vq_b200.h).
+
+torch is used for device memory and the current stream only; every computation is a kernel of
+libvq_b200.so.  Each function takes CUDA tensors, validates dtype/contiguity, and passes raw pointers.
+A CPU tensor raises: there is no fallback (SURVEY.md 8b "Device / dtype").
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import (VQ_DT_BF16, VQ_DT_F32, VQ_SEARCH_BF16, VQ_SEARCH_F32, VQ_STAT_SUM_RESID, VQ_STAT_SUM_Z, check)
+
+SEARCH_MODES = {"bf16": VQ_SEARCH_BF16, "fp32": VQ_SEARCH_F32}
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return VQ_DT_BF16
+    if t.dtype == torch.float32:
+        return VQ_DT_F32
+    raise TypeError(f"vq-vae_b200 kernels take bfloat16 or float32 latents, got {t.dtype}")
+
+
+def _need_cuda(*ts: Optional[torch.Tensor]) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("vq-vae_b200: this op runs only on CUDA tensors (sm_100a kernels, no CPU fallback); "
+                               "use oracle/vq_reference.py for CPU checks")
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _rows(z: torch.Tensor) -> Tuple[int, int, int]:
+    """[N, D] with unit inner stride -> (N, D, row stride in elements)."""
+    if z.dim() != 2 or (z.shape[1] > 1 and z.stride(1) != 1):
+        raise ValueError("expected a [N, D] tensor with contiguous rows")
+    N, D = z.shape
+    ld = z.stride(0) if N > 1 else D
+    return N, D, max(ld, D)
+
+
+def norm_elems(K: int) -> int:
+    return _lib.load().vq_norm_elems(K)
+
+
+def workspace_bytes(N: int, K: int, D: int, dtype: torch.dtype) -> int:
+    out = C.c_size_t(0)
+    dt = VQ_DT_BF16 if dtype == torch.bfloat16 else VQ_DT_F32
+    check(_lib.load().vq_workspace_bytes(N, K, D, dt, C.byref(out)), "vq_workspace_bytes")
+    return int(out.value)
+
+
+def launch_count() -> int:
+    return int(_lib.load().vq_launch_count())
+
+
+def prepare_codebook(E: torch.Tensor, search: str, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor) -> None:
+    _need_cuda(E, E_bf16, e_norm2)
+    K, D = E.shape
+    assert E.dtype == torch.float32 and E.is_contiguous()
+    assert e_norm2.dtype == torch.float32 and e_norm2.numel() >= norm_elems(K)
+    check(_lib.load().vq_prepare_codebook(_ptr(E), K, D, SEARCH_MODES[search], _ptr(E_bf16), _ptr(e_norm2),
+                                          _stream()), "vq_prepare_codebook")
+
+
+def assign(z: torch.Tensor, E: torch.Tensor, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor, search: str,
+           idx: torch.Tensor, smin: Optional[torch.Tensor], ws: Optional[torch.Tensor]) -> None:
+    _need_cuda(z, E, E_bf16, e_norm2, idx, smin, ws)
+    N, D, ld = _rows(z)
+    K = E.shape[0]
+    assert idx.dtype == torch.int32 and idx.numel() >= N and idx.is_contiguous()
+    assert smin is None or (smin.dtype == torch.float32 and smin.numel() >= N)
+    check(_lib.load().vq_assign(_ptr(z), _dt(z), N, D, ld, _ptr(E), _ptr(E_bf16), _ptr(e_norm2), K,
+                                SEARCH_MODES[search], _ptr(idx), _ptr(smin), _ptr(ws), _stream()), "vq_assign")
+
+
+def gather_st_loss_scatter(z: torch.Tensor, idx: torch.Tensor, E: torch.Tensor, q_out: torch.Tensor,
+                           sq_err_sum: torch.Tensor, code_cnt: Optional[torch.Tensor],
+                           code_sum: Optional[torch.Tensor], stat_kind: int, deterministic: bool,
+                           ws: Optional[torch.Tensor]) -> None:
+    _need_cuda(z, idx, E, q_out, sq_err_sum, code_cnt, code_sum, ws)
+    N, D, ld = _rows(z)
+    _, _, ldq = _rows(q_out)
+    K = E.shape[0]
+    assert q_out.dtype == z.dtype and q_out.shape == z.shape
+    assert idx.dtype == torch.int32 and E.dtype == torch.float32 and E.is_contiguous()
+    check(_lib.load().vq_gather_st_loss_scatter(_ptr(z), _dt(z), N, D, ld, _ptr(idx), _ptr(E), K, _ptr(q_out),
+                                                _dt(q_out), ldq, _ptr(sq_err_sum), _ptr(code_cnt), _ptr(code_sum),
+                                                stat_kind, int(bool(deterministic)), _ptr(ws), _stream()),
+          "vq_gather_st_loss_scatter")
+
+
+def ema_update(E: torch.Tensor, ema_cnt: Optional[torch.Tensor], ema_sum: Optional[torch.Tensor],
+               code_cnt: torch.Tensor, code_sum: Optional[torch.Tensor], decay: float, eps: float, do_ema: bool,
+               search: str, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor, usage_total: torch.Tensor,
+               steps_since_used: torch.Tensor, perplexity: torch.Tensor, n_dead: torch.Tensor, dead_after: int,
+               update_usage: bool, ws: torch.Tensor) -> None:
+    _need_cuda(E, ema_cnt, ema_sum, code_cnt, code_sum, E_bf16, e_norm2, usage_total, steps_since_used, perplexity,
+               n_dead, ws)
+    K, D = E.shape
+    assert usage_total.dtype == torch.int64 and steps_since_used.dtype == torch.int32 and n_dead.dtype == torch.int32
+    assert perplexity.dtype == torch.float32
+    check(_lib.load().vq_ema_update(_ptr(E), _ptr(ema_cnt), _ptr(ema_sum), _ptr(code_cnt), _ptr(code_sum), K, D,
+                                    float(decay), float(eps), int(bool(do_ema)), SEARCH_MODES[search], _ptr(E_bf16),
+                                    _ptr(e_norm2), _ptr(usage_total), _ptr(steps_since_used), _ptr(perplexity),
+                                    _ptr(n_dead), int(dead_after), int(bool(update_usage)), _ptr(ws), _stream()),
+          "vq_ema_update")
+
+
+def backward(z: torch.Tensor, q: torch.Tensor, grad_q: Optional[torch.Tensor], grad_loss: torch.Tensor, coef: float,
+             grad_z: torch.Tensor) -> None:
+    _need_cuda(z, q, grad_q, grad_loss, grad_z)
+    N, D, ld = _rows(z)
+    assert q.is_contiguous() and grad_z.is_contiguous() and (grad_q is None or grad_q.is_contiguous())
+    assert q.dtype == z.dtype and grad_z.dtype == z.dtype and (grad_q is None or grad_q.dtype == z.dtype)
+    assert grad_loss.dtype == torch.float32 and grad_loss.numel() == 1
+    check(_lib.load().vq_backward(_ptr(z), _ptr(q), _ptr(grad_q), N, D, ld, _ptr(grad_loss), float(coef),
+                                  _ptr(grad_z), _dt(z), _stream()), "vq_backward")
+
+
+def codebook_grad(resid_sum: torch.Tensor, grad_loss: torch.Tensor, coef: float, grad_E: torch.Tensor) -> None:
+    _need_cuda(resid_sum, grad_loss, grad_E)
+    K, D = resid_sum.shape
+    assert resid_sum.dtype == torch.float32 and grad_E.dtype == torch.float32 and grad_E.is_contiguous()
+    check(_lib.load().vq_codebook_grad(_ptr(resid_sum), K, D, _ptr(grad_loss), float(coef), _ptr(grad_E), _stream()),
+          "vq_codebook_grad")
+
+
+def cast_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    _need_cuda(src, dst)
+    N, D, ld = _rows(src)
+    assert src.dtype == torch.float32 and dst.dtype == torch.bfloat16 and dst.is_contiguous()
+    check(_lib.load().vq_cast_bf16(_ptr(src), N, D, ld, _ptr(dst), _stream()), "vq_cast_bf16")

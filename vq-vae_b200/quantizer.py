@@ -1,0 +1,244 @@
+"""VectorQuantizer: the ``model.quant`` object the reference scripts expect, on B200 kernels.
+
+Contract (every line below is a reference call site, the arithmetic itself is absent
+from the reference tree and follows oracle/vq_reference.py -- "parity unpinned"):
+
+  * ``VectorQuantizer(emb_dim, codebook_size, beta, quantizer in {"st","ema"}, ema_decay, ema_eps)``
+        scripts/train_vqvae.py:183-195, CLI defaults :410-414, :433-436
+  * ``.codebook`` [K, D] fp32; an ``nn.Parameter`` in "st" mode (so its qualified name contains
+    ``quant.codebook`` and lands in the weight_decay=0 AdamW group), a buffer in "ema" mode
+        scripts/train_vqvae.py:221-228 ; scripts/export_codebook.py:104,114,138
+  * ``.codebook_size`` / ``.emb_dim``                      scripts/train_vqvae.py:197
+  * ``forward(z) -> (quantized, loss, indices)``; ``.last_perplexity`` for the outer model's 5-tuple
+        scripts/train_vqvae.py:287,321,357
+  * ``attach_codebook_manager(CodebookManager(num_codes, code_dim))``   scripts/train_vqvae.py:197-198
+  * all state (codebook, EMA accumulators, usage counters) in ``state_dict()``
+        scripts/train_vqvae.py:367-373 ; scripts/export_codebook.py:124-128
+
+forward() on a CPU tensor raises: the kernels are sm_100a only and there is no fallback.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import ops, parallel
+from ._lib import VQ_STAT_SUM_RESID, VQ_STAT_SUM_Z
+
+DEFAULT_DEAD_AFTER = 100
+
+
+class CodebookManager:
+    """Usage / dead-code view over a quantiser (scripts/train_vqvae.py:92,197-198).
+
+    The reference's own class is absent; this keeps the constructor the script calls and reads the
+    counters the kernels maintain in the module's registered buffers.
+    """
+
+    def __init__(self, num_codes: int, code_dim: int):
+        self.num_codes, self.code_dim = int(num_codes), int(code_dim)
+        self.quant: Optional["VectorQuantizer"] = None
+
+    def attach(self, quant: "VectorQuantizer") -> None:
+        if (quant.codebook_size, quant.emb_dim) != (self.num_codes, self.code_dim):
+            raise ValueError("CodebookManager shape does not match the quantiser")
+        self.quant = quant
+
+    def usage(self) -> torch.Tensor:
+        return self.quant.usage_total.detach().cpu()
+
+    def dead_codes(self) -> torch.Tensor:
+        q = self.quant
+        return (q.steps_since_used >= q.dead_after).nonzero()[:, 0].cpu()
+
+    def summary(self) -> dict:
+        q = self.quant
+        return {"n_dead": int(q.n_dead), "perplexity": float(q.last_perplexity),
+                "used": int((q.usage_total > 0).sum())}
+
+
+def extract_code_usage_from_state(state: dict, prefix: str = "") -> torch.Tensor:
+    """Per-code cumulative usage from a plain state dict (scripts/export_codebook.py:124-125)."""
+    for k, v in state.items():
+        if k.startswith(prefix) and k.endswith("usage_total"):
+            return v.detach().cpu().to(torch.int64)
+    raise KeyError("no '*usage_total' entry in the state dict")
+
+
+class _VQFunction(torch.autograd.Function):
+    """Forward = search + fused gather pass (+ statistics); backward = straight-through + commitment."""
+
+    @staticmethod
+    def forward(ctx, z2: torch.Tensor, codebook: torch.Tensor, mod: "VectorQuantizer"):
+        N, D = z2.shape
+        K = mod.codebook_size
+        search = mod._search_for(z2.dtype)
+        mod._ensure_shadow(search)
+        ws = mod._workspace(N, z2.dtype)
+        idx32 = torch.empty(N, dtype=torch.int32, device=z2.device)
+        q = torch.empty((N, D), dtype=z2.dtype, device=z2.device)
+        stats = mod._stats_buffer()
+        code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
+        sqerr = torch.empty(1, dtype=torch.float32, device=z2.device)
+        E = codebook.detach()
+        ops.assign(z2, E, mod._E_bf16, mod._e_norm2, search, idx32, None, ws)
+        kind = VQ_STAT_SUM_RESID if mod.quantizer == "st" else VQ_STAT_SUM_Z
+        ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, mod.deterministic, ws)
+        w = (1.0 + mod.beta) if mod.quantizer == "st" else mod.beta
+        loss = (sqerr * (w / float(max(N * D, 1)))).reshape(())
+        ctx.save_for_backward(z2, q)
+        ctx.mod, ctx.N, ctx.D = mod, N, D
+        ctx.resid = code_sum.clone() if (mod.quantizer == "st" and codebook.requires_grad) else None
+        mod._finish_step(code_cnt, code_sum, search, ws)          # a-6 .. a-9
+        idx = idx32.to(torch.int64)
+        ctx.mark_non_differentiable(idx)
+        return q, loss, idx
+
+    @staticmethod
+    def backward(ctx, grad_q, grad_loss, _grad_idx):
+        z2, q = ctx.saved_tensors
+        mod, N, D = ctx.mod, ctx.N, ctx.D
+        dev = z2.device
+        gl = (torch.zeros(1, dtype=torch.float32, device=dev) if grad_loss is None
+              else grad_loss.detach().to(torch.float32).reshape(1))
+        grad_z = grad_E = None
+        if ctx.needs_input_grad[0]:
+            gq = None if grad_q is None else grad_q.to(z2.dtype).contiguous()
+            grad_z = torch.empty((N, D), dtype=z2.dtype, device=dev)
+            ops.backward(z2, q, gq, gl, 2.0 * mod.beta / float(max(N * D, 1)), grad_z)
+        if ctx.needs_input_grad[1] and ctx.resid is not None:
+            grad_E = torch.empty((mod.codebook_size, D), dtype=torch.float32, device=dev)
+            ops.codebook_grad(ctx.resid, gl, 2.0 / float(max(N * D, 1)), grad_E)
+        return grad_z, grad_E, None
+
+
+class VectorQuantizer(nn.Module):
+    """Nearest-codebook quantiser with straight-through output, commitment/codebook loss and (in "ema"
+    mode) an EMA codebook update, all on hand-written sm_100a kernels.
+
+    search: "auto" (bf16 latents -> bf16 tensor-core search, fp32 latents -> fp32 search), "bf16" or "fp32".
+    deterministic: code-sorted visiting order reproducible run to run (stable counting sort).
+    process_group / sync_stats: with torch.distributed initialised, per-code counts and sums are
+        all-reduced (SUM) before the EMA step so every rank applies the identical update.
+    """
+
+    def __init__(self, emb_dim: int, codebook_size: int, beta: float = 0.25, quantizer: str = "st",
+                 ema_decay: float = 0.99, ema_eps: float = 1e-5, search: str = "auto",
+                 dead_after: int = DEFAULT_DEAD_AFTER, deterministic: bool = False, process_group=None,
+                 sync_stats: bool = True):
+        super().__init__()
+        if quantizer not in ("st", "ema"):
+            raise ValueError(f"quantizer must be 'st' or 'ema', got {quantizer!r}")
+        if search not in ("auto", "bf16", "fp32"):
+            raise ValueError(f"search must be 'auto', 'bf16' or 'fp32', got {search!r}")
+        self.emb_dim, self.codebook_size = int(emb_dim), int(codebook_size)
+        self.beta, self.quantizer = float(beta), quantizer
+        self.ema_decay, self.ema_eps = float(ema_decay), float(ema_eps)
+        self.search, self.dead_after, self.deterministic = search, int(dead_after), bool(deterministic)
+        self.process_group, self.sync_stats = process_group, bool(sync_stats)
+        K, D = self.codebook_size, self.emb_dim
+        init = torch.empty(K, D, dtype=torch.float32)
+        if quantizer == "st":
+            init.uniform_(-1.0 / K, 1.0 / K)
+            self.codebook = nn.Parameter(init)
+        else:
+            init.normal_()
+            self.register_buffer("codebook", init)
+        self.register_buffer("ema_cnt", torch.ones(K, dtype=torch.float32))
+        self.register_buffer("ema_sum", init.detach().clone())
+        self.register_buffer("usage_total", torch.zeros(K, dtype=torch.int64))
+        self.register_buffer("steps_since_used", torch.zeros(K, dtype=torch.int32))
+        self.register_buffer("last_perplexity", torch.ones(1, dtype=torch.float32))
+        self.register_buffer("n_dead", torch.zeros(1, dtype=torch.int32))
+        self.manager: Optional[CodebookManager] = None
+        # scratch (never in the state dict)
+        self._E_bf16 = self._e_norm2 = self._ws = self._stats = None
+        self._shadow_key = None
+
+    # ------------------------------------------------------------------ reference-script surface
+    def attach_codebook_manager(self, manager) -> None:
+        self.manager = manager
+        if hasattr(manager, "attach"):
+            manager.attach(self)
+
+    @property
+    def perplexity(self) -> torch.Tensor:
+        return self.last_perplexity[0]
+
+    def extra_repr(self) -> str:
+        return (f"emb_dim={self.emb_dim}, codebook_size={self.codebook_size}, beta={self.beta}, "
+                f"quantizer={self.quantizer!r}, search={self.search!r}")
+
+    # ------------------------------------------------------------------ scratch management
+    def _search_for(self, dtype: torch.dtype) -> str:
+        if self.search != "auto":
+            return self.search
+        return "bf16" if dtype == torch.bfloat16 else "fp32"
+
+    def _ensure_shadow(self, search: str) -> None:
+        """(Re)build the bf16 copy and ||e||^2 the search reads if the codebook changed behind our back
+        (optimizer step in st mode, load_state_dict, .to())."""
+        E = self.codebook.detach()
+        key = (E.data_ptr(), E._version, search)
+        if key == self._shadow_key:
+            return
+        K, D = E.shape
+        if self._E_bf16 is None or self._E_bf16.device != E.device:
+            self._E_bf16 = torch.empty((K, D), dtype=torch.bfloat16, device=E.device)
+            self._e_norm2 = torch.empty(ops.norm_elems(K), dtype=torch.float32, device=E.device)
+        ops.prepare_codebook(E, search, self._E_bf16, self._e_norm2)
+        self._shadow_key = key
+
+    def _workspace(self, N: int, dtype: torch.dtype) -> torch.Tensor:
+        need = ops.workspace_bytes(N, self.codebook_size, self.emb_dim, dtype)
+        dev = self.codebook.device
+        if self._ws is None or self._ws.numel() < need or self._ws.device != dev:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        return self._ws
+
+    def _stats_buffer(self) -> torch.Tensor:
+        K, D = self.codebook_size, self.emb_dim
+        dev = self.codebook.device
+        if self._stats is None or self._stats.device != dev:
+            self._stats = torch.empty(K * D + K, dtype=torch.float32, device=dev)   # [code_sum | code_cnt]
+        return self._stats
+
+    def _dist_active(self) -> bool:
+        return self.sync_stats and parallel.dist_active(self.process_group)
+
+    # ------------------------------------------------------------------ a-6 .. a-9
+    def _finish_step(self, code_cnt, code_sum, search: str, ws) -> None:
+        ema = self.quantizer == "ema" and self.training
+        if self._dist_active():
+            if ema:      # one collective over the contiguous [sum | cnt] buffer
+                parallel.allreduce_code_stats(self._stats, self.process_group)
+            else:        # st / eval: only the counts feed usage and perplexity
+                code_cnt = parallel.allreduce_code_stats(code_cnt.clone(), self.process_group)
+        E = self.codebook.detach()
+        ops.ema_update(E, self.ema_cnt, self.ema_sum, code_cnt, code_sum, self.ema_decay, self.ema_eps, ema, search,
+                       self._E_bf16, self._e_norm2, self.usage_total, self.steps_since_used, self.last_perplexity,
+                       self.n_dead, self.dead_after, self.training, ws)
+        # the kernel refreshed the shadow for the (possibly updated) codebook
+        self._shadow_key = (E.data_ptr(), E._version, search)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, z: torch.Tensor):
+        if not z.is_cuda:
+            raise RuntimeError("VectorQuantizer.forward needs a CUDA tensor: the kernels are sm_100a only and "
+                               "there is no CPU fallback (attribute access and state_dict work on CPU)")
+        if z.shape[-1] != self.emb_dim:
+            raise ValueError(f"last dimension {z.shape[-1]} != emb_dim {self.emb_dim}")
+        with torch.autocast(device_type="cuda", enabled=False):
+            lead = z.shape[:-1]
+            in_dtype = z.dtype
+            z2 = z.reshape(-1, self.emb_dim)
+            if z2.dtype not in (torch.bfloat16, torch.float32):
+                z2 = z2.to(torch.float32)            # fp16 autocast: quantise in fp32, cast back below
+            if z2.shape[0] > 1 and (z2.stride(1) != 1 or z2.stride(0) < self.emb_dim):
+                z2 = z2.contiguous()
+            q, loss, idx = _VQFunction.apply(z2, self.codebook, self)
+            if q.dtype != in_dtype:
+                q = q.to(in_dtype)
+            return q.reshape(*lead, self.emb_dim), loss, idx.reshape(lead)
