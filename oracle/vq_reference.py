@@ -159,7 +159,7 @@ def ema_update(E: torch.Tensor, ema_cnt: torch.Tensor, ema_sum: torch.Tensor,
     Returns new (E, ema_cnt, ema_sum), fp32; arithmetic in fp32 except sum n (fp64->fp32)."""
     K = E.shape[0]
     g = torch.tensor(decay, dtype=torch.float32)
-    omg = torch.tensor(1.0 - decay, dtype=torch.float32)
+    omg = torch.tensor(1.0, dtype=torch.float32) - g          # 1 - g evaluated in fp32, like the kernel
     n = g * ema_cnt.float() + omg * cnt.float()
     m = g * ema_sum.float() + omg[None] * sums.float()
     tot = n.double().sum().to(torch.float32)
@@ -242,8 +242,8 @@ class VectorQuantizerOracle(nn.Module):
         self.register_buffer("ema_sum", init.detach().clone())
         self.register_buffer("usage_total", torch.zeros(K, dtype=torch.int64))
         self.register_buffer("steps_since_used", torch.zeros(K, dtype=torch.int32))
-        self.register_buffer("last_perplexity", torch.tensor(1.0))
-        self.register_buffer("n_dead", torch.tensor(0, dtype=torch.int32))
+        self.register_buffer("last_perplexity", torch.ones(1, dtype=torch.float32))
+        self.register_buffer("n_dead", torch.zeros(1, dtype=torch.int32))
         self.last_stats: Optional[StepStats] = None
 
     def attach_codebook_manager(self, manager) -> None:       # scripts/train_vqvae.py:197-198

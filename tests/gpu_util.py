@@ -1,0 +1,70 @@
+"""Shared helpers for the -m gpu parity tests: run one step of the CUDA path through the C ABI."""
+import torch
+
+from oracle import vq_reference as R
+from vqvae_b200 import ops
+from vqvae_b200._lib import VQ_STAT_SUM_RESID, VQ_STAT_SUM_Z
+
+
+def cuda_step(z_cpu, E_cpu, search, dtype=torch.float32, deterministic=False, stat_kind=VQ_STAT_SUM_Z, stats=True,
+              want_smin=True):
+    """assign + fused pass on the GPU.  Returns dict of CPU tensors."""
+    dev = torch.device("cuda:0")
+    z = z_cpu.to(dev).to(dtype).contiguous()
+    E = E_cpu.to(dev).float().contiguous()
+    N, D = z.shape
+    K = E.shape[0]
+    E_bf16 = torch.empty((K, D), dtype=torch.bfloat16, device=dev)
+    norms = torch.empty(ops.norm_elems(K), dtype=torch.float32, device=dev)
+    ops.prepare_codebook(E, search, E_bf16, norms)
+    ws = torch.empty(ops.workspace_bytes(N, K, D, dtype), dtype=torch.uint8, device=dev)
+    idx = torch.full((N,), -1, dtype=torch.int32, device=dev)
+    smin = torch.empty(N, dtype=torch.float32, device=dev) if want_smin else None
+    ops.assign(z, E, E_bf16, norms, search, idx, smin, ws)
+    raw_idx = idx.clone()
+    q = torch.empty_like(z)
+    sq = torch.empty(1, dtype=torch.float32, device=dev)
+    cnt = torch.empty(K, dtype=torch.float32, device=dev) if stats else None
+    sums = torch.empty((K, D), dtype=torch.float32, device=dev) if stats else None
+    ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, stat_kind, deterministic, ws)
+    torch.cuda.synchronize()
+    out = dict(idx=idx.cpu().long(), raw_idx=raw_idx.cpu().long(), q=q.cpu(), sqerr=sq.cpu()[0],
+               norms=norms.cpu(), E_bf16=E_bf16.cpu())
+    if want_smin:
+        out["smin"] = smin.cpu()
+    if stats:
+        out["cnt"], out["sums"] = cnt.cpu(), sums.cpu()
+    return out
+
+
+def check_step_against_oracle(z_cpu, E_cpu, search, dtype=torch.float32, rel=1e-5, tol=None, **kw):
+    """Full single-step parity vs the oracle.  Index rule (north_star): bit-exact except near-ties
+    (|delta d| < 1e-5 relative), which are counted and returned."""
+    prec = "bf16" if search == "bf16" else "fp32"
+    if tol is None:
+        tol = 1e-3 if dtype == torch.bfloat16 else 1e-5          # north_star tolerances
+    zin = z_cpu.to(dtype)                                        # what the kernel actually receives
+    out = cuda_step(z_cpu, E_cpu, search, dtype, **kw)
+    ref_idx, ref_dmin = R.assign(zin.float(), E_cpu, prec)
+    rep = R.near_tie_report(zin.float(), E_cpu, out["idx"], ref_idx, rel=rel, precision=prec)
+    assert rep["hard"] == 0, f"index mismatches beyond near-ties: {rep}"
+    K = E_cpu.shape[0]
+    assert int(out["idx"].min()) >= 0 and int(out["idx"].max()) < K
+    # everything downstream is checked against the oracle evaluated at the kernel's own indices, so that a
+    # legitimate near-tie flip does not fail the gather / statistics comparison
+    idx = out["idx"]
+    q_ref = R.gather(E_cpu, idx, dtype)
+    assert torch.equal(out["q"], q_ref), "gather must be bit-exact"
+    sq_ref = float(R.sq_err_sum(zin.float(), E_cpu, idx))
+    assert abs(float(out["sqerr"]) - sq_ref) <= tol * max(sq_ref, 1e-12), (float(out["sqerr"]), sq_ref)
+    if "cnt" in out:
+        cnt_ref, sums_ref = R.code_stats(zin.float(), idx, K)
+        assert torch.equal(out["cnt"], cnt_ref), "per-code counts must be exact"
+        if kw.get("stat_kind", VQ_STAT_SUM_Z) == VQ_STAT_SUM_RESID:
+            sums_ref = sums_ref - cnt_ref[:, None] * E_cpu
+            scale = (zin.float().abs().max() + E_cpu.abs().max()) * cnt_ref.clamp_min(1)[:, None]
+        else:
+            scale = zin.float().abs().max() * cnt_ref.clamp_min(1)[:, None]
+        err = ((out["sums"] - sums_ref).abs() / scale).max()
+        assert float(err) <= 1e-5, f"per-code sums off by {float(err)} (relative to |z|max * count)"
+    return rep, out
