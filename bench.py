@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py -- quantised latent vectors / second for the VQ hot path (forward + EMA), BASELINE.json's metric.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c4|c1] [--impl native|reference]
+
+One "step" = one pass of the hot path over one batch of synthetic latents: nearest-code search (a-1),
+fused gather / straight-through / loss / code statistics pass (a-2..a-5), code-stat all-reduce when N > 1
+(a-6), EMA codebook update + usage + perplexity (a-7..a-9) -- i.e. VectorQuantizer.forward in training mode,
+quantizer="ema".  Workloads:
+    c2 (default, BASELINE configs[1]): N = 256*5*32*32 = 1 310 720 vectors/GPU, K=1024, D=128, bf16
+    c4 (BASELINE configs[3])          : N = 524 288 vectors/GPU, K=8192, D=256, bf16
+    c1 (BASELINE configs[0])          : N = 40 960, K=512, D=64 (the reference-scale case)
+Weak scaling: every rank runs the same per-GPU workload on its own shard; `value` is the whole-job rate.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "c1": dict(N=8 * 5 * 32 * 32, K=512, D=64, desc="C1: 5x32x32 patch, batch 8, K=512 D=64"),
+    "c2": dict(N=256 * 5 * 32 * 32, K=1024, D=128, desc="C2: batch 256 of 5x32x32 latents, K=1024 D=128, bf16 fwd+EMA"),
+    "c4": dict(N=524288, K=8192, D=256, desc="C4: K=8192 D=256, 524288 vectors per GPU (4M per 8-GPU step)"),
+}
+METRIC = "quantised latent vectors/sec (VQ fwd+EMA)"
+UNIT = "vectors/s"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            d = json.load(fh)
+        return dict(hbm=float(d["hbm_gbs"]), tf_burst=float(d["bf16_tflops"]),
+                    tf_sust=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")   # B200_PROFILING.md fallback
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.samples, self.proc, self.thr, self.idx = [], None, None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            return
+        self.thr = threading.Thread(target=self._read, daemon=True)
+        self.thr.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_inputs(wl, rank, device, dtype=torch.bfloat16):
+    """z ~ N(0,1) seeded 1234+rank; codebook rows from the same distribution seeded 4321."""
+    g = torch.Generator(device="cpu").manual_seed(4321)
+    E = torch.randn(wl["K"], wl["D"], generator=g)
+    gz = torch.Generator(device=device).manual_seed(1234 + rank) if device != "cpu" else torch.Generator().manual_seed(1234 + rank)
+    z = torch.randn(wl["N"], wl["D"], generator=gz, device=device, dtype=torch.float32).to(dtype)
+    return z, E
+
+
+def oracle_step(R, z, E, state, K):
+    """The same step on the CPU oracle (fp32 eager torch, chunked so the [chunk, K] matrix stays small)."""
+    idx, _ = R.assign(z, E, "fp32", chunk=8192)
+    q = R.gather(E, idx, z.dtype)
+    sq = R.sq_err_sum(z, E, idx)
+    cnt, sums = R.code_stats(z, idx, K)
+    En, n, m = R.ema_update(E, state["n"], state["m"], cnt, sums, 0.99, 1e-5)
+    state["n"], state["m"] = n, m
+    R.perplexity(cnt)
+    return En, q, sq
+
+
+def cpu_baseline(wl, target_seconds=12.0):
+    """Oracle ("port") on the host cores, on a bounded sample of the same workload."""
+    from oracle import vq_reference as R
+    torch.set_num_threads(os.cpu_count() or 1)
+    sample = min(wl["N"], 65536)
+    g = torch.Generator().manual_seed(1234)
+    z = torch.randn(sample, wl["D"], generator=g)
+    E = torch.randn(wl["K"], wl["D"], generator=torch.Generator().manual_seed(4321))
+    state = {"n": torch.ones(wl["K"]), "m": E.clone()}
+    oracle_step(R, z[:4096], E, dict(state), wl["K"])          # warm-up
+    t0 = time.perf_counter(); reps = 0
+    while True:
+        E2, _, _ = oracle_step(R, z, E, state, wl["K"])
+        reps += 1
+        if time.perf_counter() - t0 > target_seconds or reps >= 50:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": sample * reps / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{reps} x {sample} vectors of the workload (K={wl['K']}, D={wl['D']}), fp32 eager torch oracle, "
+                      f"{dt:.1f} s"}
+
+
+def run_reference(args, wl):
+    """--impl reference: the reference tree has NO quantiser source, so the reference arm is the
+    CPU oracle port, all host threads, each step a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import vq_reference as R
+    torch.set_num_threads(os.cpu_count() or 1)
+    sample = min(wl["N"], 32768)
+    z = torch.randn(sample, wl["D"], generator=torch.Generator().manual_seed(1234))
+    E = torch.randn(wl["K"], wl["D"], generator=torch.Generator().manual_seed(4321))
+    state = {"n": torch.ones(wl["K"]), "m": E.clone()}
+    for _ in range(args.warmup):
+        oracle_step(R, z, E, state, wl["K"])
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle_step(R, z, E, state, wl["K"])
+    dt = time.perf_counter() - t0
+    val = sample * args.steps / dt
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "N_per_step_sampled": sample, "K": wl["K"], "D": wl["D"]},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": f"{sample} of {wl['N']} vectors per step; reference has no quantiser source, "
+                                       "oracle port timed instead"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def time_kernel(fn, iters, flush):
+    """Average device time of one launch group, CUDA events on the launching (current) stream, L2 flushed between."""
+    evs = []
+    for _ in range(iters):
+        flush()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs) / len(evs)
+
+
+def run_native(args, wl):
+    import torch.distributed as dist
+    from vqvae_b200 import VectorQuantizer, ops
+    from vqvae_b200._lib import VQ_STAT_SUM_Z
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (native arm) needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    N, K, D = wl["N"], wl["K"], wl["D"]
+    z, E = make_inputs(wl, rank, dev)
+    mod = VectorQuantizer(D, K, beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5).to(dev)
+    with torch.no_grad():
+        mod.codebook.copy_(E); mod.ema_sum.copy_(E)
+    mod.train()
+    peaks = load_peaks()
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        with torch.no_grad():
+            return mod(z)
+
+    # ---------------- value: inputs resident in HBM (335 MB of latents per step at c2 -- larger than L2)
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    clocks = ClockSampler(local); clocks.start()
+    l0 = ops.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_resident()
+    e1.record()
+    barrier()
+    launches = ops.launch_count() - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms)
+
+    # ---------------- e2e: HOST buffers through the public module call, H2D + D2H inside the timed region
+    z_host = z.cpu().pin_memory()
+    z_dev = torch.empty_like(z)
+    res_host = torch.empty(2, dtype=torch.float32).pin_memory()
+
+    def step_e2e():
+        z_dev.copy_(z_host, non_blocking=True)
+        with torch.no_grad():
+            q, loss, idx = mod(z_dev)
+        res_host[0:1].copy_(loss.reshape(1), non_blocking=True)
+        res_host[1:2].copy_(mod.last_perplexity, non_blocking=True)
+        torch.cuda.current_stream().synchronize()             # the caller reads the step's result
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(args.steps):
+        step_e2e()
+    f1.record()
+    barrier()
+    clk = clocks.stop()
+    ems = torch.tensor([f0.elapsed_time(f1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ems, op=dist.ReduceOp.MAX)
+    e2e_ms = float(ems)
+
+    # ---------------- per-kernel timing for the roofline (rank 0, timed alone, L2 flushed between launches)
+    line_extra = {}
+    if rank == 0:
+        Eb, nrm = mod._E_bf16, mod._e_norm2
+        ws = mod._workspace(N, z.dtype)
+        idx = torch.empty(N, dtype=torch.int32, device=dev)
+        q = torch.empty_like(z)
+        sq = torch.empty(1, device=dev)
+        stats = mod._stats_buffer()
+        csum, ccnt = stats[:K * D].view(K, D), stats[K * D:]
+        Ec = mod.codebook.detach()
+        flush = lambda: flush_buf.fill_(1)
+        it = max(5, min(20, args.steps))
+        t_assign = time_kernel(lambda: ops.assign(z, Ec, Eb, nrm, "bf16", idx, None, ws), it, flush)
+        t_pass = time_kernel(lambda: ops.gather_st_loss_scatter(z, idx, Ec, q, sq, ccnt, csum, VQ_STAT_SUM_Z, False, ws),
+                             it, flush)
+        flops = 2.0 * N * K * D                                   # 2*K*D per vector
+        pass_bytes = N * (D * 2 + 4 + D * 2) + K * D * 4 * 2 + K * 4   # read z + idx, write q; codebook + stats once
+        tf = flops / (t_assign * 1e-3) / 1e12
+        gbs = pass_bytes / (t_pass * 1e-3) / 1e9
+        line_extra["roofline"] = {"kernel": "assign_tc_kernel (a-1, tcgen05)", "bound": "tensor", "achieved": tf,
+                                  "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": tf / peaks["tf_burst"],
+                                  "traffic": None, "peak_source": peaks["src"] + " burst (kernel timed alone)",
+                                  "ms_per_launch": t_assign}
+        line_extra["roofline_pass"] = {"kernel": "counting sort + pass_kernel + reduce (a-2..a-5)", "bound": "hbm",
+                                       "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
+                                       "traffic": None, "peak_source": peaks["src"], "ms_per_launch": t_pass}
+        line_extra["cpu_baseline"] = cpu_baseline(wl) if world == 1 else None
+
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    n_total = N * world
+    line = {"metric": METRIC, "value": n_total * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": wl["desc"], "N_per_gpu": N, "K": K, "D": D, "quantizer": "ema",
+                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (%.0f MB of latents per step)" % (N * D * 2 / 1e6)},
+            "e2e": {"value": n_total * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": N * D * 2,
+                    "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches), "clocks": clk}
+    line.update(line_extra)
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
+    ap.add_argument("--impl", choices=["native", "reference"], default="native")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_native(args, wl)
+
+
+if __name__ == "__main__":
+    main()
