@@ -282,7 +282,7 @@ def run_native(args, wl):
         line_extra["roofline_pass"] = {"kernel": "counting sort + pass_kernel + reduce (a-2..a-5)", "bound": "hbm",
                                        "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
                                        "traffic": None, "peak_source": peaks["src"], "ms_per_launch": t_pass}
-        line_extra["cpu_baseline"] = cpu_baseline(wl) if world == 1 else None
+        line_extra["cpu_baseline"] = cpu_baseline(wl) if (world == 1 and not args.skip_cpu) else None
 
     if world > 1:
         dist.barrier()
@@ -309,6 +309,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
     ap.add_argument("--impl", choices=["native", "reference"], default="native")
+    ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     wl = WORKLOADS[args.workload]

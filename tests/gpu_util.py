@@ -59,12 +59,13 @@ def check_step_against_oracle(z_cpu, E_cpu, search, dtype=torch.float32, rel=1e-
     assert abs(float(out["sqerr"]) - sq_ref) <= tol * max(sq_ref, 1e-12), (float(out["sqerr"]), sq_ref)
     if "cnt" in out:
         cnt_ref, sums_ref = R.code_stats(zin.float(), idx, K)
+        zmax = zin.float()[R.row_is_finite(zin)].abs().max() if bool(R.row_is_finite(zin).any()) else torch.tensor(1.0)
         assert torch.equal(out["cnt"], cnt_ref), "per-code counts must be exact"
         if kw.get("stat_kind", VQ_STAT_SUM_Z) == VQ_STAT_SUM_RESID:
             sums_ref = sums_ref - cnt_ref[:, None] * E_cpu
-            scale = (zin.float().abs().max() + E_cpu.abs().max()) * cnt_ref.clamp_min(1)[:, None]
+            scale = (zmax + E_cpu.abs().max()) * cnt_ref.clamp_min(1)[:, None]
         else:
-            scale = zin.float().abs().max() * cnt_ref.clamp_min(1)[:, None]
+            scale = zmax * cnt_ref.clamp_min(1)[:, None]
         err = ((out["sums"] - sums_ref).abs() / scale).max()
         assert float(err) <= 1e-5, f"per-code sums off by {float(err)} (relative to |z|max * count)"
     return rep, out

@@ -162,12 +162,15 @@ def test_module_forward_backward_vs_oracle(quantizer, dtype):
         w = torch.randn(4, 5, 7, D, generator=g).to(dtype)
         zr = z.clone().requires_grad_(True)
         zc = z.cuda().requires_grad_(True)
+        E_before = mod.codebook.detach().clone()
         qr, lr, ir = ref(zr)
         qc, lc, ic = mod(zc)
         assert qc.shape == z.shape and ic.shape == z.shape[:-1] and ic.dtype == torch.int64 and lc.dtype == torch.float32
         rep = R.near_tie_report(z.reshape(-1, D).float(), ref.codebook.detach(), ic.cpu().reshape(-1), ir.reshape(-1))
         assert rep["mismatch"] == 0, rep      # well separated random data: expect exact agreement
-        assert torch.equal(qc.detach().cpu(), qr.detach())
+        # gather is bit-exact w.r.t. the module's own codebook; the two codebooks agree to tolerance after step 0
+        assert torch.equal(qc.detach().reshape(-1, D), E_before[ic.reshape(-1)].to(dtype))
+        np.testing.assert_allclose(qc.detach().float().cpu().numpy(), qr.detach().float().numpy(), rtol=max(tol, 1e-5), atol=1e-6)
         np.testing.assert_allclose(float(lc), float(lr), rtol=tol)
         ((qr.float() * w.float()).sum() + 2.0 * lr).backward()
         ((qc.float() * w.cuda().float()).sum() + 2.0 * lc).backward()

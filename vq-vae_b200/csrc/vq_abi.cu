@@ -74,8 +74,8 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
     VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_assign: bad in_dtype %d", in_dtype);
     VQ_REQUIRE(N >= 0 && D > 0 && K > 0 && ldz >= D, "vq_assign: bad shape N=%lld D=%d K=%d ldz=%lld", (long long)N, D,
                K, (long long)ldz);
-    VQ_REQUIRE(idx != nullptr && e_norm2 != nullptr, "vq_assign: idx and e_norm2 are required");
     if (N == 0) return VQ_OK;
+    VQ_REQUIRE(idx != nullptr && e_norm2 != nullptr, "vq_assign: idx and e_norm2 are required");
     VQ_REQUIRE(z != nullptr, "vq_assign: z is NULL");
     if (search == VQ_SEARCH_F32) {
         VQ_REQUIRE(E_f32 != nullptr, "vq_assign: E_f32 required for VQ_SEARCH_F32");
@@ -109,7 +109,7 @@ int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int
     VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_gather_st_loss_scatter: bad in_dtype %d", in_dtype);
     VQ_REQUIRE(out_dtype == in_dtype, "vq_gather_st_loss_scatter: out_dtype must equal in_dtype");
     VQ_REQUIRE(stat_kind == VQ_STAT_SUM_Z || stat_kind == VQ_STAT_SUM_RESID, "bad stat_kind %d", stat_kind);
-    VQ_REQUIRE(idx != nullptr && E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (z != nullptr && q_out != nullptr)),
+    VQ_REQUIRE(E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (idx != nullptr && z != nullptr && q_out != nullptr)),
                "vq_gather_st_loss_scatter: NULL argument");
     return launch_gather_pass(z, in_dtype, N, D, ldz, idx, E_f32, K, q_out, ldq, sq_err_sum, code_cnt, code_sum,
                               stat_kind, deterministic, ws, stream);

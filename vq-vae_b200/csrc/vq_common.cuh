@@ -48,7 +48,7 @@ void count_launch(int n = 1);
 
 // Byte offsets of the regions inside the caller-provided workspace.
 struct WsLayout {
-    size_t scal, zbf16, cnt, start, cursor, perm, partial, chunk_cnt, total;
+    size_t scal, zbf16, cnt, start, cursor, perm, partial, chunk_cnt, dpart, total;
     int rows_per_chunk, nchunks;
 };
 WsLayout ws_layout(int64_t N, int K, int D, int in_dtype);

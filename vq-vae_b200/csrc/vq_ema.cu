@@ -68,8 +68,8 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
     double h = 0.0;
     if (tot_c > 0.0)
         for (int k = t; k < K; k += 1024) {
-            const double p = (double)code_cnt[k] / tot_c;
-            h += p * log(p + 1e-10);
+            const float p = (float)((double)code_cnt[k] / tot_c);
+            h += (double)(p * logf(p + 1e-10f));
         }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);

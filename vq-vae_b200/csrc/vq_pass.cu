@@ -38,41 +38,102 @@ __global__ void hist_kernel(const int32_t* __restrict__ idx, int64_t N, int K, i
     }
 }
 
-// one block; exclusive scan of cnt[0..K) -> start[0..K], cursor[k] = start[k]
+// Shared-memory privatised variants (default path): block b owns rows [b*R, (b+1)*R); per-code counters live in
+// shared memory, so the global atomics drop from one per row to one per (block, code present in the block) and
+// hot codes no longer serialise on a single L2 address.
+__global__ void __launch_bounds__(512) hist_smem_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int R,
+                                                        int* __restrict__ cnt) {
+    extern __shared__ int sh_cnt[];
+    for (int k = threadIdx.x; k < K; k += blockDim.x) sh_cnt[k] = 0;
+    __syncthreads();
+    const int64_t a = (int64_t)blockIdx.x * R, b = min(N, a + R);
+    for (int64_t n = a + threadIdx.x; n < b; n += blockDim.x) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        atomicAdd(&sh_cnt[c], 1);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const int v = sh_cnt[k];
+        if (v != 0) atomicAdd(&cnt[k], v);
+    }
+}
+
+__global__ void __launch_bounds__(512) scatter_smem_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int R,
+                                                           int* __restrict__ cursor, int32_t* __restrict__ perm) {
+    extern __shared__ int sh[];
+    int* sh_cnt = sh;
+    int* sh_base = sh + K;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) sh_cnt[k] = 0;
+    __syncthreads();
+    const int64_t a = (int64_t)blockIdx.x * R, b = min(N, a + R);
+    for (int64_t n = a + threadIdx.x; n < b; n += blockDim.x) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        atomicAdd(&sh_cnt[c], 1);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const int v = sh_cnt[k];
+        if (v != 0) sh_base[k] = atomicAdd(&cursor[k], v);      // claim a contiguous range of code k's segment
+        sh_cnt[k] = 0;
+    }
+    __syncthreads();
+    for (int64_t n = a + threadIdx.x; n < b; n += blockDim.x) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        const int r = atomicAdd(&sh_cnt[c], 1);
+        perm[sh_base[c] + r] = (int32_t)n;
+    }
+}
+
+// one block; exclusive scan of cnt[0..K) -> start[0..K], cursor[k] = start[k].  Tiles of 4096 counters, int4 loads.
 __global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ cnt, int K, int* __restrict__ start,
                                                     int* __restrict__ cursor) {
     __shared__ int warp_tot[32];
+    __shared__ int carry_sh;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-    const int per = (K + 1023) / 1024;
-    const int a = t * per, b = min(K, a + per);
-    int s = 0;
-    for (int k = a; k < b; ++k) s += cnt[k];
-    int inc = s;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-    }
-    if (lane == 31) warp_tot[w] = inc;
+    if (t == 0) carry_sh = 0;
     __syncthreads();
-    if (w == 0) {
-        int v = warp_tot[lane], iv = v;
+    for (int base = 0; base < K; base += 4096) {
+        const int k0 = base + t * 4;
+        int v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = (k0 + j < K) ? cnt[k0 + j] : 0;
+        const int s = v[0] + v[1] + v[2] + v[3];
+        int inc = s;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int u = __shfl_up_sync(0xffffffffu, iv, o);
-            if (lane >= o) iv += u;
+            const int u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
         }
-        warp_tot[lane] = iv - v;
+        if (lane == 31) warp_tot[w] = inc;
+        __syncthreads();
+        if (w == 0) {
+            const int x = warp_tot[lane];
+            int ix = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, ix, o);
+                if (lane >= o) ix += u;
+            }
+            warp_tot[lane] = ix - x;
+        }
+        __syncthreads();
+        int run = carry_sh + warp_tot[w] + inc - s;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (k0 + j < K) {
+                start[k0 + j] = run;
+                cursor[k0 + j] = run;
+            }
+            run += v[j];
+        }
+        __syncthreads();
+        if (t == 1023) carry_sh = run;
+        __syncthreads();
     }
-    __syncthreads();
-    int run = warp_tot[w] + inc - s;
-    for (int k = a; k < b; ++k) {
-        start[k] = run;
-        cursor[k] = run;
-        run += cnt[k];
-    }
-    if (b == K && a < K) start[K] = run;
-    if (K == 0 && t == 0) start[0] = 0;
+    if (t == 0) start[K] = carry_sh;
 }
 
 __global__ void scatter_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int* __restrict__ cursor,
@@ -174,7 +235,7 @@ __global__ void __launch_bounds__(256)
 pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
             const int32_t* __restrict__ perm, const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
             float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
-            int stat_kind) {
+            float* __restrict__ dpart, int stat_kind) {
     using IO = VecIO<T>;
     constexpr int EPV = IO::EPV;
     constexpr int G = 32 / LPR;
@@ -215,18 +276,31 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     float loss = 0.f;
     int cnt = 0, cur = -1;
 
+    // Hand the finished run (cur, this 64-position slice) over.  Default: vector reds straight into code_sum.
+    // Deterministic: plain stores into slot (slice + code) of dpart -- slice and code are both non-decreasing along
+    // the sorted order and one of them changes between consecutive runs, so the slot is unique; a second kernel
+    // adds the slots of each code in slice order.
+    const int64_t slice = p0 / LG;
     auto flush = [&]() {
-        if (cur >= 0 && cnt > 0 && code_sum != nullptr) {
+        if (cur >= 0 && code_sum != nullptr && (cnt > 0 || dpart != nullptr)) {
 #pragma unroll
             for (int j = 0; j < VPL; ++j) {
                 const int v = lg + j * LPR;
                 if (v < V) {
-                    float* dst = code_sum + (int64_t)cur * D + v * EPV;
+                    if (dpart != nullptr) {
+                        float4* dst = reinterpret_cast<float4*>(dpart + (slice + cur) * D + v * EPV);
 #pragma unroll
-                    for (int x = 0; x < EPV; x += 4) red_add_v4(dst + x, acc[j][x], acc[j][x + 1], acc[j][x + 2], acc[j][x + 3]);
+                        for (int x = 0; x < EPV; x += 4)
+                            dst[x / 4] = make_float4(acc[j][x], acc[j][x + 1], acc[j][x + 2], acc[j][x + 3]);
+                    } else {
+                        float* dst = code_sum + (int64_t)cur * D + v * EPV;
+#pragma unroll
+                        for (int x = 0; x < EPV; x += 4)
+                            red_add_v4(dst + x, acc[j][x], acc[j][x + 1], acc[j][x + 2], acc[j][x + 3]);
+                    }
                 }
             }
-            if (lg == 0) atomicAdd(code_cnt + cur, (float)cnt);
+            if (lg == 0 && cnt > 0) atomicAdd(code_cnt + cur, (float)cnt);
         }
 #pragma unroll
         for (int j = 0; j < VPL; ++j)
@@ -356,6 +430,22 @@ pass_generic_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int3
     if (lane == 0) loss_partial[row < N ? row : N] = loss;   // slot N is a discard slot
 }
 
+// deterministic mode: code_sum[k] = sum over the slices that hold rows of code k, in slice order (one warp per code)
+__global__ void __launch_bounds__(256)
+reduce_dpart_kernel(const float* __restrict__ dpart, const int* __restrict__ start, int K, int D,
+                    float* __restrict__ code_sum) {
+    const int lane = threadIdx.x & 31;
+    const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (k >= K) return;
+    const int a = start[k], b = start[k + 1];
+    for (int d = lane; d < D; d += 32) {
+        float acc = 0.f;
+        if (b > a)
+            for (int sl = a / LG; sl <= (b - 1) / LG; ++sl) acc += dpart[((int64_t)sl + k) * D + d];
+        code_sum[(int64_t)k * D + d] = acc;
+    }
+}
+
 // fixed-order reduction of the per-warp partial sums (double accumulate) -> out[0]
 __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ part, int64_t n,
                                                                float* __restrict__ out) {
@@ -377,7 +467,7 @@ __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __re
 template <typename T, int VPL, int LPR>
 int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm, const float* E,
                   int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt, float* code_sum,
-                  int stat_kind, cudaStream_t st) {
+                  float* dpart, int stat_kind, cudaStream_t st) {
     constexpr int G = 32 / LPR;
     const int64_t groups = ceil_div64(N, LG);
     const int64_t warps = ceil_div64(groups, G);
@@ -385,16 +475,16 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     *nparts = blocks * 8;
     pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
                                                               static_cast<T*>(q), ldq, part, code_cnt, code_sum,
-                                                              stat_kind);
+                                                              dpart, stat_kind);
     return VQ_OK;
 }
 
 template <typename T>
 int launch_pass_dispatch(int V, const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm,
                          const float* E, int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt,
-                         float* code_sum, int stat_kind, cudaStream_t st) {
+                         float* code_sum, float* dpart, int stat_kind, cudaStream_t st) {
 #define VQ_PASS(VPL, LPR) \
-    return launch_pass_t<T, VPL, LPR>(z, N, D, ldz, idx, perm, E, K, q, ldq, part, nparts, code_cnt, code_sum, stat_kind, st)
+    return launch_pass_t<T, VPL, LPR>(z, N, D, ldz, idx, perm, E, K, q, ldq, part, nparts, code_cnt, code_sum, dpart, stat_kind, st)
     if (V <= 4) VQ_PASS(1, 4);
     if (V <= 8) VQ_PASS(1, 8);
     if (V <= 16) VQ_PASS(1, 16);
@@ -422,6 +512,7 @@ WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
     if (L.rows_per_chunk < 1024) L.rows_per_chunk = 1024;
     L.nchunks = (int)ceil_div64(N, L.rows_per_chunk);
     L.chunk_cnt = o; o += al((size_t)L.nchunks * K * 4);
+    L.dpart = o;     o += al((size_t)(ceil_div64(N, LG) + K + 1) * D * 4);   // deterministic mode: one slot per run
     L.total = o;
     return L;
 }
@@ -472,33 +563,58 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         count_launch();
     } else {
         const int32_t* perm_arg = nullptr;
+        float* dpart = nullptr;
         if (stats) {
-            const int gs = (int)(ceil_div64(N, 256) < sm_count() * 8 ? ceil_div64(N, 256) : sm_count() * 8);
             VQ_CHECK_CUDA(cudaMemsetAsync(cnt_i, 0, (size_t)K * 4, st));
-            if (deterministic) VQ_CHECK_CUDA(cudaMemsetAsync(chunk_cnt, 0, (size_t)L.nchunks * K * 4, st));
-            hist_kernel<<<gs, 256, 0, st>>>(idx, N, K, cnt_i, deterministic ? chunk_cnt : nullptr, L.rows_per_chunk);
-            scan_kernel<<<1, 1024, 0, st>>>(cnt_i, K, start, cursor);
             if (deterministic) {
+                const int gs = (int)(ceil_div64(N, 256) < sm_count() * 8 ? ceil_div64(N, 256) : sm_count() * 8);
+                VQ_CHECK_CUDA(cudaMemsetAsync(chunk_cnt, 0, (size_t)L.nchunks * K * 4, st));
+                hist_kernel<<<gs, 256, 0, st>>>(idx, N, K, cnt_i, chunk_cnt, L.rows_per_chunk);
+                scan_kernel<<<1, 1024, 0, st>>>(cnt_i, K, start, cursor);
                 chunk_offsets_kernel<<<(K + 255) / 256, 256, 0, st>>>(chunk_cnt, L.nchunks, K, start);
                 scatter_stable_kernel<<<(L.nchunks + 3) / 4, 128, 0, st>>>(idx, N, K, chunk_cnt, L.rows_per_chunk,
                                                                            L.nchunks, perm);
-                count_launch();
+                count_launch(4);
+                dpart = reinterpret_cast<float*>(w + L.dpart);
+            } else if ((size_t)K * 8 <= 200 * 1024) {
+                // shared-memory privatised counting sort: block b owns R consecutive rows
+                int R = (int)ceil_div64(N, 2 * sm_count());
+                R = round_up(R < 1024 ? 1024 : R, 1024);
+                const int nb = (int)ceil_div64(N, R);
+                static bool attr_set = false;
+                if (!attr_set) {
+                    VQ_CHECK_CUDA(cudaFuncSetAttribute(hist_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                    VQ_CHECK_CUDA(cudaFuncSetAttribute(scatter_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                    attr_set = true;
+                }
+                hist_smem_kernel<<<nb, 512, (size_t)K * 4, st>>>(idx, N, K, R, cnt_i);
+                scan_kernel<<<1, 1024, 0, st>>>(cnt_i, K, start, cursor);
+                scatter_smem_kernel<<<nb, 512, (size_t)K * 8, st>>>(idx, N, K, R, cursor, perm);
+                count_launch(3);
             } else {
+                const int gs = (int)(ceil_div64(N, 256) < sm_count() * 8 ? ceil_div64(N, 256) : sm_count() * 8);
+                hist_kernel<<<gs, 256, 0, st>>>(idx, N, K, cnt_i, nullptr, L.rows_per_chunk);
+                scan_kernel<<<1, 1024, 0, st>>>(cnt_i, K, start, cursor);
                 scatter_kernel<<<gs, 256, 0, st>>>(idx, N, K, cursor, perm);
+                count_launch(3);
             }
             VQ_CHECK_CUDA(cudaGetLastError());
-            count_launch(3);
             perm_arg = perm;
         }
         const int V = D / epv;
         if (in_dtype == VQ_DT_F32)
             launch_pass_dispatch<float>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts, code_cnt,
-                                        code_sum, stat_kind, st);
+                                        code_sum, dpart, stat_kind, st);
         else
             launch_pass_dispatch<__nv_bfloat16>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts,
-                                                code_cnt, code_sum, stat_kind, st);
+                                                code_cnt, code_sum, dpart, stat_kind, st);
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
+        if (dpart != nullptr) {
+            reduce_dpart_kernel<<<(K + 7) / 8, 256, 0, st>>>(dpart, start, K, D, code_sum);
+            VQ_CHECK_CUDA(cudaGetLastError());
+            count_launch();
+        }
     }
     reduce_partials_kernel<<<1, 1024, 0, st>>>(part, nparts, sq_err_sum);
     VQ_CHECK_CUDA(cudaGetLastError());
