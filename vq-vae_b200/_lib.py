@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvq_b200.so")
+LIB_PATH = os.environ.get("VQ_B200_LIB") or os.path.join(HERE, "libvq_b200.so")   # env: tuning variants only
 
 VQ_OK, VQ_ERR_ARG, VQ_ERR_CUDA, VQ_ERR_UNSUPPORTED = 0, 1, 2, 3
 VQ_DT_BF16, VQ_DT_F32 = 0, 1

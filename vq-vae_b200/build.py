@@ -40,6 +40,18 @@ def _digest() -> str:
     return h.hexdigest()
 
 
+def build_variant(name: str, defines) -> str:
+    """Tuning aid: compile libvq_b200_<name>.so with extra -D flags (selected at run time with VQ_B200_LIB)."""
+    out = os.path.join(HERE, f"libvq_b200_{name}.so")
+    cmd = [_nvcc()] + NVCC_FLAGS + [f"-D{d}" for d in defines] + ["-I", INCLUDE, "-o", out] + \
+          [os.path.join(CSRC, s) for s in SOURCES]
+    proc = subprocess.run(cmd, capture_output=True, text=True)
+    if proc.returncode != 0:
+        sys.stderr.write(proc.stdout + proc.stderr)
+        raise RuntimeError("nvcc failed building " + out)
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile if sources changed; returns the path of the shared library."""
     digest = _digest()
@@ -61,4 +73,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 2 and sys.argv[1] == "--variant":      # build.py --variant NAME DEF1=V DEF2=V ...
+        print(build_variant(sys.argv[2], sys.argv[3:]))
+        sys.exit(0)
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

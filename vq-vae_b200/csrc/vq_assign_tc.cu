@@ -19,6 +19,7 @@
 //              frl/config/frl_model_v0.yaml:29-33 (kind: vq, K, D).  Definition: SURVEY.md 8(a-1).
 #include <math_constants.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "vq_common.cuh"
 
@@ -32,54 +33,132 @@ constexpr int UK = 16;              // UMMA K for 16-bit inputs
 constexpr int A_KB_BYTES = BM * BK * 2;   // 16 KiB
 constexpr int B_ST_BYTES = BN * BK * 2;   // 32 KiB
 constexpr int MAX_STAGES = 8;
-constexpr int NUM_THREADS = 384;
-constexpr int NUM_EPI_WARPS = 8;
+constexpr int MAX_EPI_PARTS = 4;   // epilogue warps = 4 TMEM lane quarters x column parts (2 or 4)
 constexpr int TMEM_COLS = 512;
 constexpr int SMEM_LIMIT = 232448;  // 227 KiB opt-in maximum per CTA
+constexpr int NORM_SMEM_MAX = 8192; // codes whose ||e||^2 may be staged in shared memory (32 KiB)
 
 struct Ctl {
-    uint64_t a_full, a_empty;
+    uint64_t a_full[2], a_empty[2];
     uint64_t b_full[MAX_STAGES], b_empty[MAX_STAGES];
     uint64_t t_full[2], t_empty[2];
     uint32_t tmem_base;
     uint32_t pad;
-    float xbest[2][BM];
-    int xidx[2][BM];
+    float xbest[2][MAX_EPI_PARTS][BM];
+    int xidx[2][MAX_EPI_PARTS][BM];
 };
 
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__device__ __forceinline__ float min3f(float a, float b, float c) {
+    float d;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+// (d0, d1) = (-2, -2) * (a0, a1) + (c0, c1): one FFMA2, each half an IEEE fp32 fma (same bits as fmaf)
+__device__ __forceinline__ void score2(float& d0, float& d1, uint32_t a0, uint32_t a1, float c0, float c1) {
+    uint64_t a, c, d;
+    const uint64_t m2 = 0xC0000000C0000000ull;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "r"(a0), "r"(a1));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(c0), "f"(c1));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(m2), "l"(c));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
+
+// Fold 32 accumulator columns of one row into the running (min, argmin); lowest column wins ties, earlier chunks
+// win ties across chunks.  The comparison pipe (FMNMX / FSETP / SEL) and the power budget are the scarce resources
+// next to a saturated tensor pipe, so the common case is kept to 16 FFMA2 (scores) + 18 FMNMX3 (minimum, two new
+// values per instruction) + one compare; the index search runs only when this chunk holds a new strict minimum
+// for some lane (kHier: and then only inside the group of 8 columns that holds it).
+template <bool kNormSmem, bool kHier>
+__device__ __forceinline__ void fold_chunk(const uint32_t (&r)[32], const float* __restrict__ nrm_g, uint32_t nrm_s,
+                                           int col0, float& best, int& bidx) {
+    float s[32];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float4 n4;
+        if (kNormSmem)      // same address in every lane: one broadcast LDS.128
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(n4.x), "=f"(n4.y), "=f"(n4.z), "=f"(n4.w)
+                         : "r"(nrm_s + (uint32_t)(col0 + 4 * j) * 4u));
+        else
+            n4 = __ldg(reinterpret_cast<const float4*>(nrm_g + col0) + j);
+        score2(s[4 * j + 0], s[4 * j + 1], r[4 * j + 0], r[4 * j + 1], n4.x, n4.y);
+        score2(s[4 * j + 2], s[4 * j + 3], r[4 * j + 2], r[4 * j + 3], n4.z, n4.w);
+    }
+    float m[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        m[c] = min3f(s[8 * c], s[8 * c + 1], s[8 * c + 2]);
+        m[c] = min3f(m[c], s[8 * c + 3], s[8 * c + 4]);
+        m[c] = min3f(m[c], s[8 * c + 5], s[8 * c + 6]);
+        m[c] = fminf(m[c], s[8 * c + 7]);
+    }
+    const float mm = fminf(min3f(m[0], m[1], m[2]), m[3]);
+    if (mm < best) {
+        best = mm;
+        int jj;
+#define VQ_SEARCH8(B)                                     \
+    {                                                     \
+        jj = (B) + 7;                                     \
+        _Pragma("unroll") for (int i = 6; i >= 0; --i)    \
+            if (s[(B) + i] == mm) jj = (B) + i;           \
+    }
+        if (kHier) {        // few lanes hit per chunk (large K): look only inside the group of 8 that holds the minimum
+            if (m[0] == mm) VQ_SEARCH8(0)
+            else if (m[1] == mm) VQ_SEARCH8(8)
+            else if (m[2] == mm) VQ_SEARCH8(16)
+            else VQ_SEARCH8(24)
+        } else {            // most lanes hit in most chunks (small K): one straight-line pass, no divergence
+            jj = 31;
+#pragma unroll
+            for (int j = 30; j >= 0; --j)
+                if (s[j] == mm) jj = j;
+        }
+#undef VQ_SEARCH8
+        bidx = col0 + jj;
+    }
+}
+
+template <bool kNormSmem, int kEpiWarps, bool kHier>
+__global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
-                 const float* __restrict__ norms, int64_t N, int K, int D, int nkb, int nstages,
-                 int32_t* __restrict__ idx, float* __restrict__ smin) {
+                 const float* __restrict__ norms, int64_t N, int K, int D, int nkb, int nstages, int nabuf,
+                 int32_t* __restrict__ idx, float* __restrict__ smin, int dbg) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smA = smem;
-    uint8_t* smB = smA + nkb * A_KB_BYTES;
-    Ctl* ctl = reinterpret_cast<Ctl*>(smB + nstages * B_ST_BYTES);
+    uint8_t* smB = smA + nabuf * nkb * A_KB_BYTES;
+    const int num_nb = (K + BN - 1) / BN;
+    float* smN = reinterpret_cast<float*>(smB + nstages * B_ST_BYTES);
+    Ctl* ctl = reinterpret_cast<Ctl*>(reinterpret_cast<uint8_t*>(smN) + (kNormSmem ? num_nb * BN * 4 : 0));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int64_t ntiles = (N + BM - 1) / BM;
-    const int num_nb = (K + BN - 1) / BN;
+    const int a_bytes = nkb * A_KB_BYTES;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tm_z);
         prefetch_tmap(&tm_e);
     }
     if (warp == 1 && lane == 0) {
-        mbar_init(&ctl->a_full, 1);
-        mbar_init(&ctl->a_empty, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&ctl->a_full[b], 1);
+            mbar_init(&ctl->a_empty[b], 1);
+            mbar_init(&ctl->t_full[b], 1);
+            mbar_init(&ctl->t_empty[b], kEpiWarps);
+        }
         for (int s = 0; s < nstages; ++s) {
             mbar_init(&ctl->b_full[s], 1);
             mbar_init(&ctl->b_empty[s], 1);
         }
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&ctl->t_full[b], 1);
-            mbar_init(&ctl->t_empty[b], NUM_EPI_WARPS);
-        }
         fence_mbar_init();
     }
     if (warp == 2) tmem_alloc<TMEM_COLS>(&ctl->tmem_base);
+    if (kNormSmem && warp >= 4) {          // ||e||^2 (padded with +inf to a multiple of BN) -> shared memory, once
+        const float4* src = reinterpret_cast<const float4*>(norms);
+        float4* dst = reinterpret_cast<float4*>(smN);
+        for (int i = threadIdx.x - 128; i < num_nb * (BN / 4); i += kEpiWarps * 32) dst[i] = __ldg(src + i);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -88,14 +167,24 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
         if (elect_one()) {
-            uint32_t st = 0, ph = 0, a_ph = 0;
-            for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                mbar_wait(&ctl->a_empty, a_ph ^ 1, 1);
-                mbar_arrive_expect_tx(&ctl->a_full, nkb * A_KB_BYTES);
+            // slab number j of this CTA lives in A buffer (j % nabuf); it is that buffer's (j / nabuf)-th use
+            auto load_a = [&](uint32_t j, int64_t tile) {
+                const uint32_t buf = nabuf == 2 ? (j & 1u) : 0u;
+                const uint32_t use = nabuf == 2 ? (j >> 1) : j;
+                mbar_wait(&ctl->a_empty[buf], (use & 1u) ^ 1u, 1);
+                mbar_arrive_expect_tx(&ctl->a_full[buf], a_bytes);
                 for (int kb = 0; kb < nkb; ++kb)
-                    tma_load_2d_hint(smA + kb * A_KB_BYTES, &tm_z, &ctl->a_full, kb * BK, (int)(tile * BM),
-                                     kEvictFirst);
-                a_ph ^= 1;
+                    tma_load_2d_hint(smA + buf * a_bytes + kb * A_KB_BYTES, &tm_z, &ctl->a_full[buf], kb * BK,
+                                     (int)(tile * BM), kEvictFirst);
+            };
+            uint32_t st = 0, ph = 0, j = 0;
+            const int loads_per_slab = num_nb * nkb;
+            const int trigger = loads_per_slab < nstages ? loads_per_slab : nstages;
+            if (nabuf == 2 && (int64_t)blockIdx.x < ntiles) load_a(0, blockIdx.x);
+            for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++j) {
+                if (nabuf == 1) load_a(j, tile);
+                const int64_t next = tile + gridDim.x;
+                int issued = 0;
                 for (int nb = 0; nb < num_nb; ++nb) {
                     for (int kb = 0; kb < nkb; ++kb) {
                         mbar_wait(&ctl->b_empty[st], ph ^ 1, 2);
@@ -103,6 +192,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                         tma_load_2d_hint(smB + st * B_ST_BYTES, &tm_e, &ctl->b_full[st], kb * BK, nb * BN,
                                          kEvictLast);
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
+                        // next slab's rows: requested once this slab's first ring-full of codebook stages is in
+                        // flight, i.e. about when the previous slab retires and frees the other A buffer
+                        if (++issued == trigger && nabuf == 2 && next < ntiles) load_a(j + 1, next);
                     }
                 }
             }
@@ -112,11 +204,13 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         if (elect_one()) {
             constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
             const uint32_t a_addr = smem_u32(smA), b_addr = smem_u32(smB);
-            uint32_t st = 0, ph = 0, a_ph = 0, it = 0;
-            for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                mbar_wait(&ctl->a_full, a_ph, 3);
-                a_ph ^= 1;
+            uint32_t st = 0, ph = 0, it = 0, j = 0;
+            for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++j) {
+                const uint32_t buf = nabuf == 2 ? (j & 1u) : 0u;
+                const uint32_t use = nabuf == 2 ? (j >> 1) : j;
+                mbar_wait(&ctl->a_full[buf], use & 1u, 3);
                 tc_fence_after();
+                const uint32_t a_base = a_addr + buf * a_bytes;
                 for (int nb = 0; nb < num_nb; ++nb, ++it) {
                     const uint32_t acc = it & 1, acc_ph = (it >> 1) & 1;
                     mbar_wait(&ctl->t_empty[acc], acc_ph ^ 1, 4);
@@ -128,7 +222,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                         const int rem = D - kb * BK;
                         const int ksteps = rem >= BK ? BK / UK : (rem + UK - 1) / UK;
                         for (int k = 0; k < ksteps; ++k) {
-                            const uint64_t da = make_sdesc_sw128(a_addr + kb * A_KB_BYTES + k * (UK * 2));
+                            const uint64_t da = make_sdesc_sw128(a_base + kb * A_KB_BYTES + k * (UK * 2));
                             const uint64_t db = make_sdesc_sw128(b_addr + st * B_ST_BYTES + k * (UK * 2));
                             umma_bf16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
                         }
@@ -137,71 +231,72 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     }
                     umma_commit(&ctl->t_full[acc]);            // accumulator tile complete
                 }
-                umma_commit(&ctl->a_empty);                    // slab of z no longer read
+                umma_commit(&ctl->a_empty[buf]);               // slab of z no longer read
             }
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------------------ epilogue: running argmin
+        constexpr int PARTS = kEpiWarps / 4;          // column parts of a tile
+        constexpr int CW = BN / PARTS;                // columns per warp per tile (128 or 64)
         const int ew = warp - 4;
         const int q = ew & 3;          // TMEM lane quarter == warp % 4
-        const int half = ew >> 2;      // which 128 columns of each 256-column tile
+        const int part = ew >> 2;
+        const uint32_t nsm = smem_u32(smN);
         uint32_t it = 0, xb = 0;
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, xb ^= 1) {
-            float best[4];
-            int bi[4];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) { best[c] = CUDART_INF_F; bi[c] = 0; }
+            float best = CUDART_INF_F;
+            int bi = 0;
             for (int nb = 0; nb < num_nb; ++nb, ++it) {
                 const uint32_t acc = it & 1, acc_ph = (it >> 1) & 1;
+                const int col0 = nb * BN + part * CW;
+                const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + acc * BN + part * CW;
+                uint32_t ra[32], rb[32];
                 mbar_wait(&ctl->t_full[acc], acc_ph, 6);
                 tc_fence_after();
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    const int col0 = nb * BN + half * 128 + c * 32;
-                    const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + acc * BN + half * 128 + c * 32;
-                    uint32_t r[32];
-                    tmem_ld_32x32b_x32(taddr, r);
-                    const float4* np = reinterpret_cast<const float4*>(norms + col0);
-                    float4 nv[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) nv[j] = __ldg(np + j);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float s0 = fmaf(-2.f, __uint_as_float(r[4 * j + 0]), nv[j].x);
-                        const float s1 = fmaf(-2.f, __uint_as_float(r[4 * j + 1]), nv[j].y);
-                        const float s2 = fmaf(-2.f, __uint_as_float(r[4 * j + 2]), nv[j].z);
-                        const float s3 = fmaf(-2.f, __uint_as_float(r[4 * j + 3]), nv[j].w);
-                        const int cj = col0 + 4 * j;
-                        if (s0 < best[0]) { best[0] = s0; bi[0] = cj; }
-                        if (s1 < best[1]) { best[1] = s1; bi[1] = cj + 1; }
-                        if (s2 < best[2]) { best[2] = s2; bi[2] = cj + 2; }
-                        if (s3 < best[3]) { best[3] = s3; bi[3] = cj + 3; }
-                    }
+                if (dbg == 2) {                       // timing experiment: no TMEM read, no fold
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&ctl->t_empty[acc]);
+                    continue;
                 }
+                tmem_ld_32x32b_x32(taddr, ra);
+                tmem_ld_32x32b_x32(taddr + 32, rb);
+                tmem_wait_ld();
+                if (CW == 128) {
+                    fold_chunk<kNormSmem, kHier>(ra, norms, nsm, col0, best, bi);
+                    tmem_ld_32x32b_x32(taddr + 64, ra);          // in flight while the second chunk is folded
+                    fold_chunk<kNormSmem, kHier>(rb, norms, nsm, col0 + 32, best, bi);
+                    tmem_ld_32x32b_x32(taddr + 96, rb);
+                    tmem_wait_ld();
+                }
+                // every TMEM read of this accumulator has landed: hand it back before folding what is in registers
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ctl->t_empty[acc]);
+                if (dbg == 1) {                       // timing experiment: TMEM read but no fold
+                    bi += (int)(ra[0] ^ rb[5] ^ ra[31] ^ rb[17]);
+                    continue;
+                }
+                fold_chunk<kNormSmem, kHier>(ra, norms, nsm, col0 + CW - 64, best, bi);
+                fold_chunk<kNormSmem, kHier>(rb, norms, nsm, col0 + CW - 32, best, bi);
             }
-            float b = best[0];
-            int i = bi[0];
-#pragma unroll
-            for (int c = 1; c < 4; ++c)
-                if (best[c] < b || (best[c] == b && bi[c] < i)) { b = best[c]; i = bi[c]; }
             const int rl = q * 32 + lane;
-            if (half == 1) {
-                ctl->xbest[xb][rl] = b;
-                ctl->xidx[xb][rl] = i;
+            if (part != 0) {
+                ctl->xbest[xb][part][rl] = best;
+                ctl->xidx[xb][part][rl] = bi;
             }
-            named_bar_sync(1, NUM_EPI_WARPS * 32);
-            if (half == 0) {
-                const float ob = ctl->xbest[xb][rl];
-                const int oi = ctl->xidx[xb][rl];
-                if (ob < b || (ob == b && oi < i)) { b = ob; i = oi; }
+            named_bar_sync(1, kEpiWarps * 32);
+            if (part == 0) {
+#pragma unroll
+                for (int p = 1; p < PARTS; ++p) {     // ascending column order: strict < keeps the lowest index
+                    const float ob = ctl->xbest[xb][p][rl];
+                    const int oi = ctl->xidx[xb][p][rl];
+                    if (ob < best) { best = ob; bi = oi; }
+                }
                 const int64_t row = tile * BM + rl;
                 if (row < N) {
-                    idx[row] = i;
-                    if (smin != nullptr) smin[row] = b;
+                    idx[row] = bi;
+                    if (smin != nullptr) smin[row] = best;
                 }
             }
         }
@@ -265,10 +360,21 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     VQ_REQUIRE((reinterpret_cast<uintptr_t>(z_bf16) & 15) == 0 && (reinterpret_cast<uintptr_t>(E_bf16) & 15) == 0,
                "vq_assign(bf16): z and E_bf16 must be 16-byte aligned");
     const int nkb = (D + BK - 1) / BK;
-    int nstages = (SMEM_LIMIT - 1024 - (int)sizeof(Ctl) - nkb * A_KB_BYTES) / B_ST_BYTES;
+    const int num_nb = (K + BN - 1) / BN;
+    // shared-memory plan: [A slab x nabuf][codebook ring x nstages][||e||^2 (optional)][Ctl]
+    //   norms go to shared memory when K <= 8192 and that still leaves >= 3 ring stages;
+    //   the slab is double-buffered when that still leaves >= 4 ring stages.
+    const int avail = SMEM_LIMIT - 1024 - (int)sizeof(Ctl);
+    const int a_bytes = nkb * A_KB_BYTES;
+    const int norm_bytes = num_nb * BN * 4;
+    bool norm_smem = K <= NORM_SMEM_MAX && (avail - a_bytes - norm_bytes) / B_ST_BYTES >= 3;
+    const int after_norm = avail - (norm_smem ? norm_bytes : 0);
+    const int nabuf = (after_norm - 2 * a_bytes) / B_ST_BYTES >= 4 ? 2 : 1;
+    int nstages = (after_norm - nabuf * a_bytes) / B_ST_BYTES;
     if (nstages > 6) nstages = 6;
     VQ_REQUIRE(nstages >= 2, "vq_assign(bf16): D=%d leaves no room for the codebook ring", D);
-    const size_t smem_bytes = 1024 + (size_t)nkb * A_KB_BYTES + (size_t)nstages * B_ST_BYTES + sizeof(Ctl);
+    const size_t smem_bytes = 1024 + (size_t)nabuf * a_bytes + (size_t)nstages * B_ST_BYTES +
+                              (norm_smem ? norm_bytes : 0) + sizeof(Ctl);
 
     CUtensorMap tm_z, tm_e;
     int rc = make_tmap(&tm_z, z_bf16, N, D, ldz, BM);
@@ -276,14 +382,23 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     rc = make_tmap(&tm_e, E_bf16, K, D, D, BN);
     if (rc != VQ_OK) return rc;
 
-    static bool attr_set = false;
-    if (!attr_set) {
-        VQ_CHECK_CUDA(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-        attr_set = true;
+    static int epi_warps = 0, dbg = 0;
+    if (epi_warps == 0) {
+        const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // tuning knob: 8 or 16 epilogue warps
+        epi_warps = (ev != nullptr && atoi(ev) == 8) ? 8 : 16;
+        ev = getenv("VQ_ASSIGN_DBG");                            // 1/2: timing experiments, results are WRONG
+        if (ev != nullptr) dbg = atoi(ev);
     }
     const int64_t ntiles = (N + BM - 1) / BM;
     const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
-    assign_tc_kernel<<<grid, NUM_THREADS, smem_bytes, st>>>(tm_z, tm_e, e_norm2, N, K, D, nkb, nstages, idx, smin);
+    void (*kern)(const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int, int32_t*, float*, int);
+    const bool hier = K >= 4096;       // measured on B200: C4 (K=8192) 1.52 ms vs 1.53 ms, C2 (K=1024) 0.386 ms vs 0.365 ms
+#define VQ_PICK(NS, EW) (hier ? assign_tc_kernel<NS, EW, true> : assign_tc_kernel<NS, EW, false>)
+    if (norm_smem) kern = epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
+    else kern = epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
+#undef VQ_PICK
+    VQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    kern<<<grid, 128 + 32 * epi_warps, smem_bytes, st>>>(tm_z, tm_e, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg);
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

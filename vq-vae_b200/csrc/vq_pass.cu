@@ -230,6 +230,33 @@ template <> struct VecIO<float> {
 
 // T: storage type of z and q.  LPR lanes cooperate on one row (16 bytes per lane per vector), VPL vectors per lane.
 // perm == nullptr visits rows in natural order (no statistics wanted: eval mode).
+//
+// Latent rows reach the SM through a per-thread cp.async ring in shared memory (STAGES batches of UB rows): every
+// thread copies exactly the 16-byte pieces it will later consume, so cp.async.wait_group is the only
+// synchronisation, no registers are tied up by loads in flight, and (STAGES - 1) * UB rows per lane group are
+// outstanding at any time -- memory-level parallelism independent of occupancy.
+#ifndef VQ_PASS_STAGES
+#define VQ_PASS_STAGES 4
+#endif
+#ifndef VQ_PASS_ROWS
+#define VQ_PASS_ROWS 4
+#endif
+constexpr int PASS_STAGES = VQ_PASS_STAGES;
+// rows per batch: VQ_PASS_ROWS 16-byte pieces per thread per batch
+template <int VPL> struct PassCfg { static constexpr int U = VQ_PASS_ROWS / VPL > 1 ? VQ_PASS_ROWS / VPL : 1; };
+
+__device__ __forceinline__ void cp_async_16(uint32_t smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
+__device__ __forceinline__ int4 lds_16(uint32_t addr) {
+    int4 r;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+    return r;
+}
+
 template <typename T, int VPL, int LPR>
 __global__ void __launch_bounds__(256)
 pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
@@ -239,10 +266,16 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     using IO = VecIO<T>;
     constexpr int EPV = IO::EPV;
     constexpr int G = 32 / LPR;
-    constexpr int IDS = LG / LPR;
-    constexpr int U = VPL == 1 ? 8 : (VPL == 2 ? 4 : 2);
-    static_assert(LPR % U == 0 || U % LPR == 0, "batching");
-    constexpr int UB = U < LPR ? U : LPR;             // rows fetched per batch
+    constexpr int U = PassCfg<VPL>::U;
+    constexpr int UB = U < LPR ? U : LPR;             // rows per batch
+    constexpr int NB = LG / UB;                       // batches per lane group
+    constexpr int S = PASS_STAGES;
+    static_assert(LG % UB == 0 && NB >= S, "batching");
+
+    extern __shared__ int4 pass_smem[];
+    // [S][UB][VPL][256] 16-byte ring slots, then per warp [G][LG] row numbers and [G][LG] codes
+    const uint32_t ring = smem_u32(pass_smem) + threadIdx.x * 16u;
+    int* pos_base = reinterpret_cast<int*>(pass_smem + S * UB * VPL * 256) + (threadIdx.x >> 5) * (2 * G * LG);
 
     const int lane = threadIdx.x & 31;
     const int g = lane / LPR, lg = lane % LPR;
@@ -250,10 +283,11 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     const int64_t warp_global = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t p0 = (warp_global * G + g) * LG;
     const int V = D / EPV;
+    int* prow = pos_base + g * LG;
+    int* pcode = pos_base + (G + g) * LG;
 
-    int rows[IDS], codes[IDS];
 #pragma unroll
-    for (int i = 0; i < IDS; ++i) {
+    for (int i = 0; i < LG / LPR; ++i) {
         const int64_t pos = p0 + i * LPR + lg;
         int r = -1, c = -1;
         if (pos < N) {
@@ -261,8 +295,28 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
             c = idx[r];
             if ((unsigned)c >= (unsigned)K) c = 0;
         }
-        rows[i] = r;
-        codes[i] = c;
+        prow[i * LPR + lg] = r;
+        pcode[i * LPR + lg] = c;
+    }
+    __syncwarp();
+
+    auto issue = [&](int b) {                         // batch b of this lane group -> ring stage b % S
+        const int stage = b % S;
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int r = prow[b * UB + u];
+#pragma unroll
+            for (int j = 0; j < VPL; ++j) {
+                const int v = lg + j * LPR;
+                if (r >= 0 && v < V)
+                    cp_async_16(ring + (uint32_t)(((stage * UB + u) * VPL + j) * 256) * 16u, z + (int64_t)r * ldz + v * EPV);
+            }
+        }
+    };
+#pragma unroll
+    for (int b = 0; b < S - 1; ++b) {
+        issue(b);
+        cp_async_commit();
     }
 
     float e[VPL][EPV], acc[VPL][EPV];
@@ -309,79 +363,75 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
         cnt = 0;
     };
 
-#pragma unroll
-    for (int i = 0; i < IDS; ++i) {
 #pragma unroll 1
-        for (int l0 = 0; l0 < LPR; l0 += UB) {
-            int rr[UB], cc[UB];
-            int4 zv[UB][VPL];
+    for (int b = 0; b < NB; ++b) {
+        if (b + S - 1 < NB) issue(b + S - 1);
+        cp_async_commit();                            // (possibly empty) group keeps the wait distance constant
+        cp_async_wait<S - 1>();                       // batch b has landed in this thread's slots
+        const int stage = b % S;
 #pragma unroll
-            for (int u = 0; u < UB; ++u) {
-                rr[u] = __shfl_sync(0xffffffffu, rows[i], g * LPR + l0 + u);
-                cc[u] = __shfl_sync(0xffffffffu, codes[i], g * LPR + l0 + u);
+        for (int u = 0; u < UB; ++u) {
+            const int r = prow[b * UB + u];
+            const int c = pcode[b * UB + u];
+            const bool valid = r >= 0;
+            int4 zv[VPL];
+            bool nf = false;
 #pragma unroll
-                for (int j = 0; j < VPL; ++j) {
-                    const int v = lg + j * LPR;
-                    zv[u][j] = make_int4(0, 0, 0, 0);
-                    if (rr[u] >= 0 && v < V) zv[u][j] = ld_stream_16(z + (int64_t)rr[u] * ldz + v * EPV);
-                }
+            for (int j = 0; j < VPL; ++j) {
+                const int v = lg + j * LPR;
+                zv[j] = make_int4(0, 0, 0, 0);
+                if (valid && v < V) zv[j] = lds_16(ring + (uint32_t)(((stage * UB + u) * VPL + j) * 256) * 16u);
+                nf |= IO::nonfinite(zv[j]);
             }
+            const bool bad = (__ballot_sync(0xffffffffu, valid && nf) & gmask) != 0;
+            if (valid) {
+                if (c != cur) {
+                    flush();
+                    cur = c;
 #pragma unroll
-            for (int u = 0; u < UB; ++u) {
-                const bool valid = rr[u] >= 0;
-                bool nf = false;
+                    for (int j = 0; j < VPL; ++j) {
+                        const int v = lg + j * LPR;
+                        if (v < V) {
+                            const float4* src = reinterpret_cast<const float4*>(E + (int64_t)cur * D + v * EPV);
 #pragma unroll
-                for (int j = 0; j < VPL; ++j) nf |= IO::nonfinite(zv[u][j]);
-                const bool bad = (__ballot_sync(0xffffffffu, valid && nf) & gmask) != 0;
-                if (valid) {
-                    if (cc[u] != cur) {
-                        flush();
-                        cur = cc[u];
-#pragma unroll
-                        for (int j = 0; j < VPL; ++j) {
-                            const int v = lg + j * LPR;
-                            if (v < V) {
-                                const float4* src = reinterpret_cast<const float4*>(E + (int64_t)cur * D + v * EPV);
-#pragma unroll
-                                for (int x = 0; x < EPV; x += 4) {
-                                    const float4 t = __ldg(src + x / 4);
-                                    e[j][x] = t.x; e[j][x + 1] = t.y; e[j][x + 2] = t.z; e[j][x + 3] = t.w;
-                                }
-                                qv[j] = IO::pack(e[j]);
+                            for (int x = 0; x < EPV; x += 4) {
+                                const float4 t = __ldg(src + x / 4);
+                                e[j][x] = t.x; e[j][x + 1] = t.y; e[j][x + 2] = t.z; e[j][x + 3] = t.w;
                             }
+                            qv[j] = IO::pack(e[j]);
                         }
                     }
-                    if (!bad) {
+                }
+                if (!bad) {
 #pragma unroll
-                        for (int j = 0; j < VPL; ++j) {
-                            const int v = lg + j * LPR;
-                            if (v < V) {
-                                float zf[EPV];
-                                IO::unpack(zv[u][j], zf);
+                    for (int j = 0; j < VPL; ++j) {
+                        const int v = lg + j * LPR;
+                        if (v < V) {
+                            float zf[EPV];
+                            IO::unpack(zv[j], zf);
 #pragma unroll
-                                for (int x = 0; x < EPV; ++x) {
-                                    const float d = zf[x] - e[j][x];
-                                    loss = fmaf(d, d, loss);
-                                    acc[j][x] += stat_kind == VQ_STAT_SUM_RESID ? d : zf[x];
-                                }
-                                st_stream_16(q + (int64_t)rr[u] * ldq + v * EPV, qv[j]);
+                            for (int x = 0; x < EPV; ++x) {
+                                const float d = zf[x] - e[j][x];
+                                loss = fmaf(d, d, loss);
+                                acc[j][x] += stat_kind == VQ_STAT_SUM_RESID ? d : zf[x];
                             }
+                            st_stream_16(q + (int64_t)r * ldq + v * EPV, qv[j]);
                         }
-                        ++cnt;
-                    } else {
-                        // non-finite latent row: idx := 0, q := E[0], no contribution to loss or statistics
-#pragma unroll
-                        for (int j = 0; j < VPL; ++j) {
-                            const int v = lg + j * LPR;
-                            if (v < V) {
-                                float e0[EPV];
-#pragma unroll
-                                for (int x = 0; x < EPV; ++x) e0[x] = __ldg(E + v * EPV + x);
-                                st_stream_16(q + (int64_t)rr[u] * ldq + v * EPV, IO::pack(e0));
-                            }
-                        }
-                        if (lg == 0) idx[rr[u]] = 0;
                     }
+                    ++cnt;
+                } else {
+                    // non-finite latent row: idx := 0, q := E[0], no contribution to loss or statistics
+#pragma unroll
+                    for (int j = 0; j < VPL; ++j) {
+                        const int v = lg + j * LPR;
+                        if (v < V) {
+                            float e0[EPV];
+#pragma unroll
+                            for (int x = 0; x < EPV; ++x) e0[x] = __ldg(E + v * EPV + x);
+                            st_stream_16(q + (int64_t)r * ldq + v * EPV, IO::pack(e0));
+                        }
+                    }
+                    if (lg == 0) idx[r] = 0;
                 }
             }
         }
@@ -473,7 +523,15 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     const int64_t warps = ceil_div64(groups, G);
     const int64_t blocks = ceil_div64(warps, 8);
     *nparts = blocks * 8;
-    pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
+    constexpr int U = PassCfg<VPL>::U;
+    constexpr int UB = U < LPR ? U : LPR;
+    const size_t smem = (size_t)PASS_STAGES * UB * VPL * 256 * 16 + (size_t)8 * 2 * G * LG * sizeof(int);
+    static bool attr_set = false;              // one flag per template instance
+    if (!attr_set) {
+        cudaFuncSetAttribute(pass_kernel<T, VPL, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = true;
+    }
+    pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, smem, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
                                                               static_cast<T*>(q), ldq, part, code_cnt, code_sum,
                                                               dpart, stat_kind);
     return VQ_OK;
