@@ -107,6 +107,10 @@ int vq_codebook_grad(const float* resid_sum, int K, int D, const float* grad_los
 /* fp32 -> bf16 row cast used when fp32 latents go through VQ_SEARCH_BF16 (dst is [N, D] dense). */
 int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_stream_t stream);
 
+/* a-0 layout ingest: batched transpose src [B, R, C] -> dst [B, C, R] (dense, dtype VQ_DT_*).  Channel-first latents
+ * [B, D, S] (frl/models/representation.py:317-334) -> rows [B*S, D]: R = D, C = S; quantised rows back: R = S, C = D. */
+int vq_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, vq_stream_t stream);
+
 /* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
 int64_t vq_launch_count(void);
 

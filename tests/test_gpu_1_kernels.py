@@ -222,3 +222,39 @@ def test_module_eval_mode_and_empty_and_state_dict_roundtrip(tmp_path):
     cpu = VectorQuantizer(16, 40, quantizer="ema")
     cpu.load_state_dict(sd)
     assert torch.equal(cpu.codebook, E1.cpu()) and cpu.codebook.shape[0] == 40
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,dtype", [((3, 64, 17, 19), torch.float32), ((2, 128, 5, 32, 32), torch.bfloat16),
+                                         ((4, 7, 9), torch.float32), ((1, 256, 130), torch.bfloat16)])
+def test_layout_transpose_matches_permute(shape, dtype):
+    """a-0: [B, R, C] -> [B, C, R] kernel, bit-exact against torch.permute (odd sizes take the scalar path)."""
+    from vqvae_b200 import ops
+    x = torch.randn(shape).to(dtype).cuda().reshape(shape[0], shape[1], -1)
+    out = torch.empty((x.shape[0], x.shape[2], x.shape[1]), dtype=dtype, device="cuda")
+    ops.layout_transpose(x, out)
+    assert torch.equal(out, x.permute(0, 2, 1).contiguous())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_channel_first_module_matches_channel_last(dtype):
+    """The live model's [B, D, H, W] latents through channel_first=True == permuting by hand (values and grads)."""
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(3)
+    D, K = 64, 128
+    a = VectorQuantizer(D, K, quantizer="ema", channel_first=True, deterministic=True).cuda()
+    b = VectorQuantizer(D, K, quantizer="ema", deterministic=True).cuda()
+    b.load_state_dict(a.state_dict())
+    z = torch.randn(2, D, 24, 20).to(dtype).cuda()
+    za = z.clone().requires_grad_(True)
+    zb = z.permute(0, 2, 3, 1).contiguous().requires_grad_(True)
+    qa, la, ia = a(za)
+    qb, lb, ib = b(zb)
+    assert qa.shape == z.shape and ia.shape == (2, 24, 20)
+    assert torch.equal(ia, ib) and torch.equal(qa, qb.permute(0, 3, 1, 2)) and float(la) == float(lb)
+    w = torch.randn_like(qa)
+    (qa * w).sum().backward(retain_graph=True); la.backward()
+    (qb * w.permute(0, 2, 3, 1)).sum().backward(retain_graph=True); lb.backward()
+    assert torch.equal(za.grad, zb.grad.permute(0, 3, 1, 2))
+    assert torch.equal(a.codebook, b.codebook)

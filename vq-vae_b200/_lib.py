@@ -34,6 +34,7 @@ SIGNATURES = {
     "vq_backward": (_i, [_p, _p, _p, _i64, _i, _i64, _p, _f, _p, _i, _p]),
     "vq_codebook_grad": (_i, [_p, _i, _i, _p, _f, _p, _p]),
     "vq_cast_bf16": (_i, [_p, _i64, _i, _i64, _p, _p]),
+    "vq_layout_transpose": (_i, [_p, _p, _i64, _i64, _i64, _i, _p]),
 }
 
 

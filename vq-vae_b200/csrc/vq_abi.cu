@@ -145,4 +145,10 @@ int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_s
     return launch_cast_bf16(src, N, D, ld, dst, stream);
 }
 
+int vq_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, vq_stream_t stream) {
+    VQ_REQUIRE(dtype == VQ_DT_BF16 || dtype == VQ_DT_F32, "vq_layout_transpose: bad dtype %d", dtype);
+    VQ_REQUIRE((B == 0 || R == 0 || C == 0) || (src != nullptr && dst != nullptr), "vq_layout_transpose: NULL argument");
+    return launch_layout_transpose(src, dst, B, R, C, dtype, stream);
+}
+
 }  // extern "C"

@@ -43,6 +43,7 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
 int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32,
                        const float* e_norm2, int K, int32_t* idx, float* smin, cudaStream_t st);
 int launch_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, cudaStream_t st);
+int launch_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, cudaStream_t st);
 bool assign_tc_supported(int64_t N, int D, int64_t ldz, int K);
 void count_launch(int n = 1);
 

@@ -141,3 +141,11 @@ def cast_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
     N, D, ld = _rows(src)
     assert src.dtype == torch.float32 and dst.dtype == torch.bfloat16 and dst.is_contiguous()
     check(_lib.load().vq_cast_bf16(_ptr(src), N, D, ld, _ptr(dst), _stream()), "vq_cast_bf16")
+
+
+def layout_transpose(src: torch.Tensor, dst: torch.Tensor) -> None:
+    """src [B, R, C] -> dst [B, C, R], both dense (a-0: channel-first <-> row layout)."""
+    _need_cuda(src, dst)
+    B, R, C = src.shape
+    assert src.is_contiguous() and dst.is_contiguous() and dst.shape == (B, C, R) and dst.dtype == src.dtype
+    check(_lib.load().vq_layout_transpose(_ptr(src), _ptr(dst), B, R, C, _dt(src), _stream()), "vq_layout_transpose")

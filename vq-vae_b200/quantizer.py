@@ -114,12 +114,32 @@ class _VQFunction(torch.autograd.Function):
         return grad_z, grad_E, None
 
 
+class _LayoutTranspose(torch.autograd.Function):
+    """[B, R, C] -> [B, C, R] on the library's transpose kernel (a-0); the backward is the same kernel the other way."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor):
+        B, R, C = x.shape
+        out = torch.empty((B, C, R), dtype=x.dtype, device=x.device)
+        ops.layout_transpose(x.contiguous(), out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g: torch.Tensor):
+        B, C, R = g.shape
+        out = torch.empty((B, R, C), dtype=g.dtype, device=g.device)
+        ops.layout_transpose(g.contiguous(), out)
+        return out
+
+
 class VectorQuantizer(nn.Module):
     """Nearest-codebook quantiser with straight-through output, commitment/codebook loss and (in "ema"
     mode) an EMA codebook update, all on hand-written sm_100a kernels.
 
     search: "auto" (bf16 latents -> bf16 tensor-core search, fp32 latents -> fp32 search), "bf16" or "fp32".
     deterministic: code-sorted visiting order reproducible run to run (stable counting sort).
+    channel_first: forward takes [B, D, *spatial] (the live model's layout, frl/models/representation.py:317-334)
+        and returns quantized in the same layout, indices [B, *spatial]; one transpose pass each way (a-0).
     process_group / sync_stats: with torch.distributed initialised, per-code counts and sums are
         all-reduced (SUM) before the EMA step so every rank applies the identical update.
     """
@@ -127,7 +147,7 @@ class VectorQuantizer(nn.Module):
     def __init__(self, emb_dim: int, codebook_size: int, beta: float = 0.25, quantizer: str = "st",
                  ema_decay: float = 0.99, ema_eps: float = 1e-5, search: str = "auto",
                  dead_after: int = DEFAULT_DEAD_AFTER, deterministic: bool = False, process_group=None,
-                 sync_stats: bool = True):
+                 sync_stats: bool = True, channel_first: bool = False):
         super().__init__()
         if quantizer not in ("st", "ema"):
             raise ValueError(f"quantizer must be 'st' or 'ema', got {quantizer!r}")
@@ -138,6 +158,7 @@ class VectorQuantizer(nn.Module):
         self.ema_decay, self.ema_eps = float(ema_decay), float(ema_eps)
         self.search, self.dead_after, self.deterministic = search, int(dead_after), bool(deterministic)
         self.process_group, self.sync_stats = process_group, bool(sync_stats)
+        self.channel_first = bool(channel_first)
         K, D = self.codebook_size, self.emb_dim
         init = torch.empty(K, D, dtype=torch.float32)
         if quantizer == "st":
@@ -170,6 +191,39 @@ class VectorQuantizer(nn.Module):
     def extra_repr(self) -> str:
         return (f"emb_dim={self.emb_dim}, codebook_size={self.codebook_size}, beta={self.beta}, "
                 f"quantizer={self.quantizer!r}, search={self.search!r}")
+
+    # ------------------------------------------------------------------ codebook maintenance (host-driven, rare)
+    @torch.no_grad()
+    def init_codebook_from(self, z: torch.Tensor, generator: Optional[torch.Generator] = None) -> None:
+        """Data-dependent initialisation: K rows of z (sampled without replacement when N >= K) become the
+        codebook; EMA accumulators restart at n = 1, m = E.  Call on every rank with the SAME rows (or
+        broadcast the codebook afterwards).  Not part of the per-step path; plain torch indexing."""
+        rows = z.detach().reshape(-1, self.emb_dim).to(torch.float32)
+        N, K = rows.shape[0], self.codebook_size
+        pick = (torch.randperm(N, generator=generator, device=rows.device)[:K] if N >= K
+                else torch.randint(0, N, (K,), generator=generator, device=rows.device))
+        self.codebook.data.copy_(rows[pick].to(self.codebook.device))
+        self.ema_sum.copy_(self.codebook.data)
+        self.ema_cnt.fill_(1.0)
+        self._shadow_key = None
+
+    @torch.no_grad()
+    def reseed_dead_codes(self, z: torch.Tensor, generator: Optional[torch.Generator] = None) -> int:
+        """Optional dead-code policy (off unless the caller invokes it): every code with
+        steps_since_used >= dead_after is replaced by a random row of z.  Returns how many were replaced."""
+        dead = (self.steps_since_used >= self.dead_after).nonzero()[:, 0]
+        n = int(dead.numel())
+        if n == 0:
+            return 0
+        rows = z.detach().reshape(-1, self.emb_dim).to(torch.float32)
+        pick = torch.randint(0, rows.shape[0], (n,), generator=generator, device=rows.device)
+        new = rows[pick].to(self.codebook.device)
+        self.codebook.data[dead] = new
+        self.ema_sum[dead] = new
+        self.ema_cnt[dead] = 1.0
+        self.steps_since_used[dead] = 0
+        self._shadow_key = None
+        return n
 
     # ------------------------------------------------------------------ scratch management
     def _search_for(self, dtype: torch.dtype) -> str:
@@ -228,6 +282,8 @@ class VectorQuantizer(nn.Module):
         if not z.is_cuda:
             raise RuntimeError("VectorQuantizer.forward needs a CUDA tensor: the kernels are sm_100a only and "
                                "there is no CPU fallback (attribute access and state_dict work on CPU)")
+        if self.channel_first:
+            return self._forward_channel_first(z)
         if z.shape[-1] != self.emb_dim:
             raise ValueError(f"last dimension {z.shape[-1]} != emb_dim {self.emb_dim}")
         with torch.autocast(device_type="cuda", enabled=False):
@@ -242,3 +298,19 @@ class VectorQuantizer(nn.Module):
             if q.dtype != in_dtype:
                 q = q.to(in_dtype)
             return q.reshape(*lead, self.emb_dim), loss, idx.reshape(lead)
+
+    def _forward_channel_first(self, z: torch.Tensor):
+        if z.dim() < 2 or z.shape[1] != self.emb_dim:
+            raise ValueError(f"channel_first: dimension 1 is {tuple(z.shape)[1:2]}, expected emb_dim {self.emb_dim}")
+        with torch.autocast(device_type="cuda", enabled=False):
+            B, D, spatial = z.shape[0], z.shape[1], z.shape[2:]
+            in_dtype = z.dtype
+            z3 = z.reshape(B, D, -1)
+            if z3.dtype not in (torch.bfloat16, torch.float32):
+                z3 = z3.to(torch.float32)
+            rows = _LayoutTranspose.apply(z3)                          # [B, S, D]
+            q, loss, idx = _VQFunction.apply(rows.reshape(-1, D), self.codebook, self)
+            qcf = _LayoutTranspose.apply(q.reshape(B, -1, D))          # [B, D, S]
+            if qcf.dtype != in_dtype:
+                qcf = qcf.to(in_dtype)
+            return qcf.reshape(B, D, *spatial), loss, idx.reshape(B, *spatial)
