@@ -38,6 +38,16 @@ METRIC = "quantised latent vectors/sec (VQ fwd+EMA)"
 UNIT = "vectors/s"
 
 
+def load_traffic(workload_key, kernel):
+    """Measured DRAM bytes per launch of `kernel` (ncu --set full capture, committed under profiles/), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as fh:
+            return json.load(fh).get(workload_key, {}).get(kernel)
+    except Exception:
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -277,11 +287,15 @@ def run_native(args, wl):
         gbs = pass_bytes / (t_pass * 1e-3) / 1e9
         line_extra["roofline"] = {"kernel": "assign_tc_kernel (a-1, tcgen05)", "bound": "tensor", "achieved": tf,
                                   "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": tf / peaks["tf_burst"],
-                                  "traffic": None, "peak_source": peaks["src"] + " burst (kernel timed alone)",
+                                  "traffic": load_traffic(args.workload, "assign_tc_kernel"),
+                                  "algorithmic_bytes": N * (D * 2 + 4) + K * D * 2 + K * 4,
+                                  "peak_source": peaks["src"] + " burst (kernel timed alone)",
                                   "ms_per_launch": t_assign}
-        line_extra["roofline_pass"] = {"kernel": "counting sort + pass_kernel + reduce (a-2..a-5)", "bound": "hbm",
+        line_extra["roofline_pass"] = {"kernel": "counting sort (memset, hist, scan+scatter) + pass_kernel (a-2..a-5)", "bound": "hbm",
                                        "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
-                                       "traffic": None, "peak_source": peaks["src"], "ms_per_launch": t_pass}
+                                       "traffic": load_traffic(args.workload, "pass_kernel"),
+                                       "algorithmic_bytes": pass_bytes, "peak_source": peaks["src"],
+                                       "ms_per_launch": t_pass}
         line_extra["cpu_baseline"] = cpu_baseline(wl) if (world == 1 and not args.skip_cpu) else None
 
     if world > 1:

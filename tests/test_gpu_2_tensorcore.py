@@ -150,3 +150,61 @@ def test_full_size_properties_c2():
     ref_idx, _ = R.assign(z[sel.cuda()].cpu().float(), E0.cpu(), "bf16")
     rep = R.near_tie_report(z[sel.cuda()].cpu().float(), E0.cpu(), idx[sel.cuda()].cpu(), ref_idx, precision="bf16")
     assert rep["hard"] == 0, rep
+
+
+@pytest.mark.gpu
+def test_full_size_properties_c4():
+    """BASELINE config C4 per-GPU shard at full size (N = 524288, K = 8192, D = 256, bf16)."""
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(1)
+    N, K, D = 524288, 8192, 256
+    mod = VectorQuantizer(D, K, quantizer="ema").cuda()
+    E0 = mod.codebook.clone()
+    ema_sum0, ema_cnt0 = mod.ema_sum.clone(), mod.ema_cnt.clone()
+    z = torch.randn(N, D, device="cuda", dtype=torch.bfloat16)
+    q, loss, idx = mod(z)
+    assert int(idx.min()) >= 0 and int(idx.max()) < K
+    assert torch.equal(q, E0[idx].to(torch.bfloat16))
+    assert int(mod.usage_total.sum()) == N
+    assert torch.equal(mod.usage_total, torch.bincount(idx, minlength=K))           # counts are exact
+    # linearity of the EMA statistics: sum over codes of sum_k == column sums of z (checksum of checksums)
+    code_sum = (mod.ema_sum - 0.99 * ema_sum0) / (1.0 - 0.99)
+    np.testing.assert_allclose(code_sum.sum(0).cpu().numpy(), z.float().sum(0).cpu().numpy(), rtol=2e-3, atol=2.0)
+    code_cnt = (mod.ema_cnt - 0.99 * ema_cnt0) / (1.0 - 0.99)
+    np.testing.assert_allclose(code_cnt.cpu().numpy(), mod.usage_total.float().cpu().numpy(), rtol=1e-3, atol=0.05)
+    mse = float(((z.float() - E0[idx]) ** 2).mean())
+    assert abs(float(loss) / 0.25 - mse) < 1e-4 * mse
+    sel = torch.randperm(N)[:2048]
+    zs = z[sel.cuda()].cpu().float()
+    ref_idx, _ = R.assign(zs, E0.cpu(), "bf16")
+    rep = R.near_tie_report(zs, E0.cpu(), idx[sel.cuda()].cpu(), ref_idx, precision="bf16")
+    assert rep["hard"] == 0, rep
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("K,D", [(256, 128), (256, 64), (512, 64)])
+def test_reference_default_sizes_bf16(K, D):
+    """The sizes the reference itself writes down (scripts/config.yaml:48-49, frl/config/frl_model_v0.yaml:32-33,
+    scripts/train_vqvae.py:410-411): epilogue-bound shapes, full single-step parity vs the oracle."""
+    g = torch.Generator().manual_seed(K + D)
+    E = torch.randn(K, D, generator=g)
+    z = E[torch.randint(0, K, (20000,), generator=g)] + 0.3 * torch.randn(20000, D, generator=g)
+    from gpu_util import check_step_against_oracle
+    rep, _ = check_step_against_oracle(z, E, "bf16", dtype=torch.bfloat16)
+    assert rep["hard"] == 0, rep
+
+
+@pytest.mark.gpu
+def test_fp16_autocast_input_is_quantised_in_fp32():
+    """scripts/train_vqvae.py:284-286 runs the model under fp16 autocast unless --bf16: half latents are widened."""
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(5)
+    mod = VectorQuantizer(32, 64, quantizer="st").cuda()
+    z = torch.randn(4, 10, 32, device="cuda", dtype=torch.float16, requires_grad=True)
+    with torch.autocast("cuda", dtype=torch.float16):
+        q, loss, idx = mod(z)
+    assert q.dtype == torch.float16 and loss.dtype == torch.float32 and idx.shape == (4, 10)
+    ref_idx, _ = R.assign(z.detach().float().cpu().reshape(-1, 32), mod.codebook.detach().cpu(), "fp32")
+    assert torch.equal(idx.cpu().reshape(-1), ref_idx)
+    (q.float().sum() + loss).backward()
+    assert torch.isfinite(z.grad).all() and mod.codebook.grad is not None

@@ -67,11 +67,22 @@ __device__ __forceinline__ void score2(float& d0, float& d1, uint32_t a0, uint32
 // win ties across chunks.  The comparison pipe (FMNMX / FSETP / SEL) and the power budget are the scarce resources
 // next to a saturated tensor pipe, so the common case is kept to 16 FFMA2 (scores) + 18 FMNMX3 (minimum, two new
 // values per instruction) + one compare; the index search runs only when this chunk holds a new strict minimum
-// for some lane (kHier: and then only inside the group of 8 columns that holds it).
-template <bool kNormSmem, bool kHier>
+// for some lane.  kMode selects what happens then:
+//   0  straight-line compare/select search over the 32 columns (always exact, 62 ALU instructions)
+//   1  the same search restricted to the group of 8 columns that holds the minimum (pays off when few lanes hit)
+//   2  DEFERRED: the lane only parks the winning group of 8 scores in its private shared-memory slot (two predicated
+//      STS.128) and remembers the group's first column in bidx; the within-group search happens once per slab in
+//      finish_deferred().  With K/32 chunks against 32 rows per warp nearly every chunk is a hit for some lane when
+//      K is small, so this takes the per-chunk hit cost from ~68 to ~18 issue slots and leaves the comparison pipe
+//      to the minimum itself.
+template <bool kNormSmem, int kMode>
 __device__ __forceinline__ void fold_chunk(const uint32_t (&r)[32], const float* __restrict__ nrm_g, uint32_t nrm_s,
-                                           int col0, float& best, int& bidx) {
+                                           int col0, float& best, int& bidx, uint32_t slot, uint32_t slot_stride, int dbg = 0) {
     float s[32];
+    if (dbg == 3) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s[j] = __uint_as_float(r[j]);
+    } else
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         float4 n4;
@@ -93,6 +104,28 @@ __device__ __forceinline__ void fold_chunk(const uint32_t (&r)[32], const float*
         m[c] = fminf(m[c], s[8 * c + 7]);
     }
     const float mm = fminf(min3f(m[0], m[1], m[2]), m[3]);
+    if (kMode == 2) {
+        const bool hit = mm < best;
+        const bool p0 = hit && m[0] == mm;
+        const bool p1 = hit && !p0 && m[1] == mm;
+        const bool p2 = hit && !p0 && !p1 && m[2] == mm;
+        const bool p3 = hit && !p0 && !p1 && !p2;
+#define VQ_PARK(P, B)                                                                                            \
+    if (P) {                                                                                                     \
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "f"(s[(B)]), "f"(s[(B) + 1]),       \
+                     "f"(s[(B) + 2]), "f"(s[(B) + 3]) : "memory");                                               \
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(slot + slot_stride), "f"(s[(B) + 4]),      \
+                     "f"(s[(B) + 5]), "f"(s[(B) + 6]), "f"(s[(B) + 7]) : "memory");                              \
+        bidx = col0 + (B);                                                                                       \
+    }
+        VQ_PARK(p0, 0)
+        VQ_PARK(p1, 8)
+        VQ_PARK(p2, 16)
+        VQ_PARK(p3, 24)
+#undef VQ_PARK
+        if (hit) best = mm;
+        return;
+    }
     if (mm < best) {
         best = mm;
         int jj;
@@ -102,7 +135,7 @@ __device__ __forceinline__ void fold_chunk(const uint32_t (&r)[32], const float*
         _Pragma("unroll") for (int i = 6; i >= 0; --i)    \
             if (s[(B) + i] == mm) jj = (B) + i;           \
     }
-        if (kHier) {        // few lanes hit per chunk (large K): look only inside the group of 8 that holds the minimum
+        if (kMode == 1) {   // few lanes hit per chunk (large K): look only inside the group of 8 that holds the minimum
             if (m[0] == mm) VQ_SEARCH8(0)
             else if (m[1] == mm) VQ_SEARCH8(8)
             else if (m[2] == mm) VQ_SEARCH8(16)
@@ -118,7 +151,21 @@ __device__ __forceinline__ void fold_chunk(const uint32_t (&r)[32], const float*
     }
 }
 
-template <bool kNormSmem, int kEpiWarps, bool kHier>
+// kMode 2: resolve the parked group of 8 scores into the column index (once per slab and row)
+__device__ __forceinline__ int finish_deferred(float best, int bcol, uint32_t slot, uint32_t slot_stride) {
+    float v[8];
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(slot));
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "r"(slot + slot_stride));
+    int i = 7;
+#pragma unroll
+    for (int j = 6; j >= 0; --j)
+        if (v[j] == best) i = j;
+    return best < CUDART_INF_F ? bcol + i : 0;       // no hit at all (every score NaN / +inf): index 0
+}
+
+template <bool kNormSmem, int kEpiWarps, int kMode>
 __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
                  const float* __restrict__ norms, int64_t N, int K, int D, int nkb, int nstages, int nabuf,
@@ -129,7 +176,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     uint8_t* smB = smA + nabuf * nkb * A_KB_BYTES;
     const int num_nb = (K + BN - 1) / BN;
     float* smN = reinterpret_cast<float*>(smB + nstages * B_ST_BYTES);
-    Ctl* ctl = reinterpret_cast<Ctl*>(reinterpret_cast<uint8_t*>(smN) + (kNormSmem ? num_nb * BN * 4 : 0));
+    uint8_t* smP = reinterpret_cast<uint8_t*>(smN) + (kNormSmem ? num_nb * BN * 4 : 0);   // kMode 2: parked groups
+    Ctl* ctl = reinterpret_cast<Ctl*>(smP + (kMode == 2 ? 2 * kEpiWarps * 32 * 16 : 0));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -242,6 +290,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         const int q = ew & 3;          // TMEM lane quarter == warp % 4
         const int part = ew >> 2;
         const uint32_t nsm = smem_u32(smN);
+        const uint32_t slot = smem_u32(smP) + (threadIdx.x - 128) * 16u;     // [2][epilogue threads] x 16 B: conflict-free
+        constexpr uint32_t slot_stride = kEpiWarps * 32 * 16;
         uint32_t it = 0, xb = 0;
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, xb ^= 1) {
             float best = CUDART_INF_F;
@@ -263,9 +313,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                 tmem_ld_32x32b_x32(taddr + 32, rb);
                 tmem_wait_ld();
                 if (CW == 128) {
-                    fold_chunk<kNormSmem, kHier>(ra, norms, nsm, col0, best, bi);
+                    fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0, best, bi, slot, slot_stride, dbg);
                     tmem_ld_32x32b_x32(taddr + 64, ra);          // in flight while the second chunk is folded
-                    fold_chunk<kNormSmem, kHier>(rb, norms, nsm, col0 + 32, best, bi);
+                    fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + 32, best, bi, slot, slot_stride, dbg);
                     tmem_ld_32x32b_x32(taddr + 96, rb);
                     tmem_wait_ld();
                 }
@@ -277,9 +327,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     bi += (int)(ra[0] ^ rb[5] ^ ra[31] ^ rb[17]);
                     continue;
                 }
-                fold_chunk<kNormSmem, kHier>(ra, norms, nsm, col0 + CW - 64, best, bi);
-                fold_chunk<kNormSmem, kHier>(rb, norms, nsm, col0 + CW - 32, best, bi);
+                fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0 + CW - 64, best, bi, slot, slot_stride, dbg);
+                fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + CW - 32, best, bi, slot, slot_stride, dbg);
             }
+            if (kMode == 2) bi = finish_deferred(best, bi, slot, slot_stride);
             const int rl = q * 32 + lane;
             if (part != 0) {
                 ctl->xbest[xb][part][rl] = best;
@@ -392,13 +443,25 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     const int64_t ntiles = (N + BM - 1) / BM;
     const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
     void (*kern)(const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int, int32_t*, float*, int);
-    const bool hier = K >= 4096;       // measured on B200: C4 (K=8192) 1.52 ms vs 1.53 ms, C2 (K=1024) 0.386 ms vs 0.365 ms
-#define VQ_PICK(NS, EW) (hier ? assign_tc_kernel<NS, EW, true> : assign_tc_kernel<NS, EW, false>)
+    // what happens when a chunk holds a new minimum (see fold_chunk): large K -> search inside the group of 8 at once;
+    // small K -> park the group in shared memory and search once per slab (needs 16 KiB of shared memory).
+    //   measured on B200: C4 (K=8192) mode 1 1.52 ms vs mode 0 1.53 ms; C2 (K=1024) mode 0 0.365 ms, mode 1 0.386 ms
+    static int mode_override = -1;
+    {
+        const char* ev = getenv("VQ_ASSIGN_MODE");
+        if (ev != nullptr) mode_override = atoi(ev);
+    }
+    int mode = K >= 4096 ? 1 : 2;
+    if (mode_override >= 0 && mode_override <= 2) mode = mode_override;
+    const size_t park_bytes = (size_t)2 * epi_warps * 32 * 16;
+    if (mode == 2 && smem_bytes + park_bytes > (size_t)SMEM_LIMIT) mode = 0;
+    const size_t smem_total = smem_bytes + (mode == 2 ? park_bytes : 0);
+#define VQ_PICK(NS, EW) (mode == 2 ? assign_tc_kernel<NS, EW, 2> : mode == 1 ? assign_tc_kernel<NS, EW, 1> : assign_tc_kernel<NS, EW, 0>)
     if (norm_smem) kern = epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
     else kern = epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
 #undef VQ_PICK
     VQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    kern<<<grid, 128 + 32 * epi_warps, smem_bytes, st>>>(tm_z, tm_e, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg);
+    kern<<<grid, 128 + 32 * epi_warps, smem_total, st>>>(tm_z, tm_e, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg);
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

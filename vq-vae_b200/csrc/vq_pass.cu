@@ -87,6 +87,86 @@ __global__ void __launch_bounds__(512) scatter_smem_kernel(const int32_t* __rest
     }
 }
 
+// Fused variant used by the default path: every block first rebuilds the exclusive scan of the (complete) global
+// histogram in its own shared memory -- K counters, a few microseconds, in parallel on all blocks -- which removes
+// the single-block scan launch from the critical path; `cursor` starts at zero and holds the claimed count per code.
+// The blocks also clear the statistics the pass will accumulate into (code_sum, code_cnt), replacing two memsets.
+__global__ void __launch_bounds__(512)
+scan_scatter_smem_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int R, const int* __restrict__ cnt,
+                         int* __restrict__ cursor, int32_t* __restrict__ perm, float4* __restrict__ zero_a, int64_t na4,
+                         float* __restrict__ zero_b, int nb) {
+    extern __shared__ int sh[];
+    int* sh_cnt = sh;
+    int* sh_base = sh + K;
+    int* sh_start = sh + 2 * K;
+    __shared__ int warp_tot[16];
+    __shared__ int carry_sh;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+
+    for (int64_t i = (int64_t)blockIdx.x * 512 + t; i < na4; i += (int64_t)gridDim.x * 512)
+        zero_a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = blockIdx.x * 512 + t; i < nb; i += gridDim.x * 512) zero_b[i] = 0.f;
+
+    if (t == 0) carry_sh = 0;
+    for (int k = t; k < K; k += 512) sh_cnt[k] = 0;
+    __syncthreads();
+    for (int base = 0; base < K; base += 2048) {          // exclusive scan, 4 counters per thread per tile
+        const int k0 = base + t * 4;
+        int v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = (k0 + j < K) ? cnt[k0 + j] : 0;
+        const int sum4 = v[0] + v[1] + v[2] + v[3];
+        int inc = sum4;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        if (lane == 31) warp_tot[w] = inc;
+        __syncthreads();
+        if (w == 0) {
+            const int x = lane < 16 ? warp_tot[lane] : 0;
+            int ix = x;
+#pragma unroll
+            for (int o = 1; o < 16; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, ix, o);
+                if (lane >= o) ix += u;
+            }
+            if (lane < 16) warp_tot[lane] = ix - x;
+        }
+        __syncthreads();
+        int run = carry_sh + warp_tot[w] + inc - sum4;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (k0 + j < K) sh_start[k0 + j] = run;
+            run += v[j];
+        }
+        __syncthreads();
+        if (t == 511) carry_sh = run;
+        __syncthreads();
+    }
+
+    const int64_t a = (int64_t)blockIdx.x * R, b = min(N, a + R);
+    for (int64_t n = a + t; n < b; n += 512) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        atomicAdd(&sh_cnt[c], 1);
+    }
+    __syncthreads();
+    for (int k = t; k < K; k += 512) {
+        const int v = sh_cnt[k];
+        if (v != 0) sh_base[k] = sh_start[k] + atomicAdd(&cursor[k], v);   // contiguous range inside code k's segment
+        sh_cnt[k] = 0;
+    }
+    __syncthreads();
+    for (int64_t n = a + t; n < b; n += 512) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        const int r = atomicAdd(&sh_cnt[c], 1);
+        perm[sh_base[c] + r] = (int32_t)n;
+    }
+}
+
 // one block; exclusive scan of cnt[0..K) -> start[0..K], cursor[k] = start[k].  Tiles of 4096 counters, int4 loads.
 __global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ cnt, int K, int* __restrict__ start,
                                                     int* __restrict__ cursor) {
@@ -262,7 +342,7 @@ __global__ void __launch_bounds__(256)
 pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
             const int32_t* __restrict__ perm, const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
             float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
-            float* __restrict__ dpart, int stat_kind) {
+            float* __restrict__ dpart, int stat_kind, int* __restrict__ done, float* __restrict__ sq_err_out) {
     using IO = VecIO<T>;
     constexpr int EPV = IO::EPV;
     constexpr int G = 32 / LPR;
@@ -439,6 +519,32 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     flush();
     loss = warp_sum(loss);
     if (lane == 0) loss_partial[warp_global] = loss;
+
+    // The block that finishes last adds the per-warp partial sums in a fixed order (double accumulate): no extra
+    // launch, and the result does not depend on which block happens to be last.
+    __shared__ bool is_last;
+    __shared__ double red[8];
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = atomicAdd(done, 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        const int64_t nparts = (int64_t)gridDim.x * 8;
+        double acc_d = 0.0;
+        for (int64_t i = threadIdx.x; i < nparts; i += 256) acc_d += (double)__ldcg(loss_partial + i);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc_d += __shfl_xor_sync(0xffffffffu, acc_d, o);
+        if (lane == 0) red[threadIdx.x >> 5] = acc_d;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double tot = 0.0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) tot += red[i];
+            sq_err_out[0] = (float)tot;
+            *done = 0;
+        }
+    }
 }
 
 // any D / alignment: one warp per row, scalar accesses, plain atomics.  Correct but slow; only odd shapes land here.
@@ -517,7 +623,7 @@ __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __re
 template <typename T, int VPL, int LPR>
 int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm, const float* E,
                   int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt, float* code_sum,
-                  float* dpart, int stat_kind, cudaStream_t st) {
+                  float* dpart, int stat_kind, int* done, float* sq_err, cudaStream_t st) {
     constexpr int G = 32 / LPR;
     const int64_t groups = ceil_div64(N, LG);
     const int64_t warps = ceil_div64(groups, G);
@@ -533,16 +639,16 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     }
     pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, smem, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
                                                               static_cast<T*>(q), ldq, part, code_cnt, code_sum,
-                                                              dpart, stat_kind);
+                                                              dpart, stat_kind, done, sq_err);
     return VQ_OK;
 }
 
 template <typename T>
 int launch_pass_dispatch(int V, const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm,
                          const float* E, int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt,
-                         float* code_sum, float* dpart, int stat_kind, cudaStream_t st) {
+                         float* code_sum, float* dpart, int stat_kind, int* done, float* sq_err, cudaStream_t st) {
 #define VQ_PASS(VPL, LPR) \
-    return launch_pass_t<T, VPL, LPR>(z, N, D, ldz, idx, perm, E, K, q, ldq, part, nparts, code_cnt, code_sum, dpart, stat_kind, st)
+    return launch_pass_t<T, VPL, LPR>(z, N, D, ldz, idx, perm, E, K, q, ldq, part, nparts, code_cnt, code_sum, dpart, stat_kind, done, sq_err, st)
     if (V <= 4) VQ_PASS(1, 4);
     if (V <= 8) VQ_PASS(1, 8);
     if (V <= 16) VQ_PASS(1, 16);
@@ -561,9 +667,9 @@ WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
     size_t o = 0;
     L.scal = o;      o += 256;
     L.zbf16 = o;     o += in_dtype == VQ_DT_F32 ? al((size_t)N * D * 2) : 0;
-    L.cnt = o;       o += al((size_t)K * 4);
+    L.cnt = o;       o += al((size_t)(2 * K + 4) * 4);     // [histogram K | cursor K | done counter]: one memset
+    L.cursor = L.cnt + (size_t)K * 4;
     L.start = o;     o += al((size_t)(K + 1) * 4);
-    L.cursor = o;    o += al((size_t)K * 4);
     L.perm = o;      o += al((size_t)N * 4);
     L.partial = o;   o += al((size_t)(N + 64) * 4);       // generic kernel: one slot per row (+ discard slot)
     L.rows_per_chunk = (int)((ceil_div64(N, 256) + 31) / 32 * 32);
@@ -582,11 +688,11 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                "vq_gather_st_loss_scatter: bad shape N=%lld D=%d K=%d", (long long)N, D, K);
     VQ_REQUIRE((code_cnt == nullptr) == (code_sum == nullptr), "code_cnt and code_sum must both be given or both NULL");
     const bool stats = code_cnt != nullptr;
-    if (stats) {
-        VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
-        VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
-    }
     if (N == 0) {
+        if (stats) {
+            VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
+            VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
+        }
         VQ_CHECK_CUDA(cudaMemsetAsync(sq_err_sum, 0, 4, st));
         return VQ_OK;
     }
@@ -596,9 +702,13 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     int* cnt_i = reinterpret_cast<int*>(w + L.cnt);
     int* start = reinterpret_cast<int*>(w + L.start);
     int* cursor = reinterpret_cast<int*>(w + L.cursor);
+    int* done = cnt_i + 2 * K;
     int32_t* perm = reinterpret_cast<int32_t*>(w + L.perm);
     float* part = reinterpret_cast<float*>(w + L.partial);
     int* chunk_cnt = reinterpret_cast<int*>(w + L.chunk_cnt);
+    // histogram, cursor and the pass kernel's completion counter are cleared by ONE memset
+    VQ_CHECK_CUDA(cudaMemsetAsync(cnt_i, 0, (size_t)(2 * K + 1) * 4, st));
+    bool stats_cleared = false;
 
     const int es = in_dtype == VQ_DT_F32 ? 4 : 2;
     const int epv = 16 / es;
@@ -609,6 +719,10 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     if (!vec_ok) {
         const int64_t blocks = ceil_div64(N, 8);
         nparts = N;
+        if (stats) {
+            VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
+            VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
+        }
         if (in_dtype == VQ_DT_F32)
             pass_generic_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const float*>(z), N, D, ldz, idx,
                                                                          E_f32, K, static_cast<float*>(q_out), ldq,
@@ -623,7 +737,6 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         const int32_t* perm_arg = nullptr;
         float* dpart = nullptr;
         if (stats) {
-            VQ_CHECK_CUDA(cudaMemsetAsync(cnt_i, 0, (size_t)K * 4, st));
             if (deterministic) {
                 const int gs = (int)(ceil_div64(N, 256) < sm_count() * 8 ? ceil_div64(N, 256) : sm_count() * 8);
                 VQ_CHECK_CUDA(cudaMemsetAsync(chunk_cnt, 0, (size_t)L.nchunks * K * 4, st));
@@ -634,21 +747,25 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                                                                            L.nchunks, perm);
                 count_launch(4);
                 dpart = reinterpret_cast<float*>(w + L.dpart);
-            } else if ((size_t)K * 8 <= 200 * 1024) {
-                // shared-memory privatised counting sort: block b owns R consecutive rows
+            } else if ((size_t)K * 12 <= 200 * 1024 && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 &&
+                       ((size_t)K * D) % 4 == 0) {
+                // shared-memory privatised counting sort, 2 launches: block b owns R consecutive rows; the second
+                // kernel rebuilds the scan per block and clears code_sum / code_cnt on the way
                 int R = (int)ceil_div64(N, 2 * sm_count());
                 R = round_up(R < 1024 ? 1024 : R, 1024);
                 const int nb = (int)ceil_div64(N, R);
                 static bool attr_set = false;
                 if (!attr_set) {
                     VQ_CHECK_CUDA(cudaFuncSetAttribute(hist_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-                    VQ_CHECK_CUDA(cudaFuncSetAttribute(scatter_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                    VQ_CHECK_CUDA(cudaFuncSetAttribute(scan_scatter_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
                     attr_set = true;
                 }
                 hist_smem_kernel<<<nb, 512, (size_t)K * 4, st>>>(idx, N, K, R, cnt_i);
-                scan_kernel<<<1, 1024, 0, st>>>(cnt_i, K, start, cursor);
-                scatter_smem_kernel<<<nb, 512, (size_t)K * 8, st>>>(idx, N, K, R, cursor, perm);
-                count_launch(3);
+                scan_scatter_smem_kernel<<<nb, 512, (size_t)K * 12, st>>>(idx, N, K, R, cnt_i, cursor, perm,
+                                                                          reinterpret_cast<float4*>(code_sum),
+                                                                          (int64_t)K * D / 4, code_cnt, K);
+                count_launch(2);
+                stats_cleared = true;
             } else {
                 const int gs = (int)(ceil_div64(N, 256) < sm_count() * 8 ? ceil_div64(N, 256) : sm_count() * 8);
                 hist_kernel<<<gs, 256, 0, st>>>(idx, N, K, cnt_i, nullptr, L.rows_per_chunk);
@@ -658,14 +775,18 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
             }
             VQ_CHECK_CUDA(cudaGetLastError());
             perm_arg = perm;
+            if (!stats_cleared) {
+                VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
+                VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
+            }
         }
         const int V = D / epv;
         if (in_dtype == VQ_DT_F32)
             launch_pass_dispatch<float>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts, code_cnt,
-                                        code_sum, dpart, stat_kind, st);
+                                        code_sum, dpart, stat_kind, done, sq_err_sum, st);
         else
             launch_pass_dispatch<__nv_bfloat16>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts,
-                                                code_cnt, code_sum, dpart, stat_kind, st);
+                                                code_cnt, code_sum, dpart, stat_kind, done, sq_err_sum, st);
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
         if (dpart != nullptr) {
@@ -673,6 +794,7 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
             VQ_CHECK_CUDA(cudaGetLastError());
             count_launch();
         }
+        return VQ_OK;                       // sq_err_sum was written by the pass kernel's last block
     }
     reduce_partials_kernel<<<1, 1024, 0, st>>>(part, nparts, sq_err_sum);
     VQ_CHECK_CUDA(cudaGetLastError());
