@@ -53,7 +53,8 @@ enum {
 int vq_abi_version(void);
 const char* vq_last_error(void);
 
-/* Number of floats the e_norm2 array must hold: K rounded up to the search kernel's code tile (padding = +inf). */
+/* Number of floats the e_norm2 array must hold: K_pad = K rounded up to the search kernel's 256-code tile norms
+ * (padding = +inf) followed by K_pad * 8 floats of search-private data (-||e||^2/2 as a tensor-core operand image). */
 int vq_norm_elems(int K);
 
 /* Scratch bytes for one step at these sizes (covers vq_assign and vq_gather_st_loss_scatter). */

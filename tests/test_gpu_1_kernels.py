@@ -141,7 +141,14 @@ def test_ema_update_kernel_vs_oracle():
     np.testing.assert_allclose(float(ppl), float(R.perplexity(cnt)), rtol=1e-5)
     assert torch.equal(Eb.cpu(), dE.cpu().to(torch.bfloat16))
     np.testing.assert_allclose(nrm.cpu()[:K].numpy(), R.code_norms(dE.cpu(), "bf16").numpy(), rtol=1e-5)
-    assert torch.isinf(nrm.cpu()[K:]).all()
+    Kp = (K + 255) // 256 * 256                      # norms are padded to the 256-code search tile with +inf
+    assert torch.isinf(nrm.cpu()[K:Kp]).all()
+    # behind them: -||e||^2/2 split into three bf16 pieces per code, as an 8 KiB no-swizzle UMMA operand image per tile
+    img = nrm.cpu()[Kp:].view(torch.bfloat16).view(Kp // 256, 32, 2, 8, 8).float()      # [tile, group, khalf, row, elem]
+    h = img[:, :, 0, :, :3].sum(-1).reshape(-1)                                          # per code: h1 + h2 + h3
+    np.testing.assert_allclose(h[:K].numpy(), -0.5 * nrm.cpu()[:K].numpy(), rtol=3e-7)
+    assert torch.isinf(h[K:]).all() and bool((h[K:] < 0).all())
+    assert float(img[:, :, 1].abs().max()) == 0.0 and float(img[:, :, 0, :, 3:].abs().max()) == 0.0
 
 
 @pytest.mark.parametrize("quantizer", ["st", "ema"])

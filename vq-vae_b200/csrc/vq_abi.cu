@@ -51,7 +51,8 @@ int vq_abi_version(void) { return VQ_ABI_VERSION; }
 const char* vq_last_error(void) { return g_err; }
 int64_t vq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
-int vq_norm_elems(int K) { return K <= 0 ? 0 : round_up(K, 256); }
+// K_pad fp32 norms followed by the K_pad x 32 B "aug" image (vq_ema.cu: write_aug)
+int vq_norm_elems(int K) { return K <= 0 ? 0 : round_up(K, 256) * 9; }
 
 int vq_workspace_bytes(int64_t N, int K, int D, int in_dtype, size_t* out_bytes) {
     VQ_REQUIRE(out_bytes != nullptr, "vq_workspace_bytes: out_bytes is NULL");

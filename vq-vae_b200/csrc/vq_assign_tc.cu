@@ -151,8 +151,49 @@ __device__ __forceinline__ void fold_chunk(const uint32_t (&r)[32], const float*
     }
 }
 
-// kMode 2: resolve the parked group of 8 scores into the column index (once per slab and row)
-__device__ __forceinline__ int finish_deferred(float best, int bcol, uint32_t slot, uint32_t slot_stride) {
+__device__ __forceinline__ float max3f(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+// kMode 3 ("aug"): the accumulator already holds t = z.e - ||e||^2/2 (the norm rode through the tensor core as one more
+// K step), so the nearest code is the ARG-MAX of the raw accumulator: no norm loads, no FFMA -- 18 FMNMX3 plus the
+// parking of the winning group of 8 (see kMode 2).  nbest is the running maximum.
+__device__ __forceinline__ void fold_chunk_aug(const uint32_t (&r)[32], int col0, float& nbest, int& bidx, uint32_t slot,
+                                               uint32_t slot_stride) {
+    float m[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        m[c] = max3f(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1]), __uint_as_float(r[8 * c + 2]));
+        m[c] = max3f(m[c], __uint_as_float(r[8 * c + 3]), __uint_as_float(r[8 * c + 4]));
+        m[c] = max3f(m[c], __uint_as_float(r[8 * c + 5]), __uint_as_float(r[8 * c + 6]));
+        m[c] = fmaxf(m[c], __uint_as_float(r[8 * c + 7]));
+    }
+    const float mm = fmaxf(max3f(m[0], m[1], m[2]), m[3]);
+    const bool hit = mm > nbest;
+    const bool p0 = hit && m[0] == mm;
+    const bool p1 = hit && !p0 && m[1] == mm;
+    const bool p2 = hit && !p0 && !p1 && m[2] == mm;
+    const bool p3 = hit && !p0 && !p1 && !p2;
+#define VQ_PARK(P, B)                                                                                              \
+    if (P) {                                                                                                       \
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "r"(r[(B)]), "r"(r[(B) + 1]),         \
+                     "r"(r[(B) + 2]), "r"(r[(B) + 3]) : "memory");                                                 \
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(slot + slot_stride), "r"(r[(B) + 4]),        \
+                     "r"(r[(B) + 5]), "r"(r[(B) + 6]), "r"(r[(B) + 7]) : "memory");                                \
+        bidx = col0 + (B);                                                                                         \
+    }
+    VQ_PARK(p0, 0)
+    VQ_PARK(p1, 8)
+    VQ_PARK(p2, 16)
+    VQ_PARK(p3, 24)
+#undef VQ_PARK
+    if (hit) nbest = mm;
+}
+
+// kMode 2 / 3: resolve the parked group of 8 scores into the column index (once per slab and row)
+__device__ __forceinline__ int finish_deferred(float best, int bcol, uint32_t slot, uint32_t slot_stride, bool any_hit) {
     float v[8];
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(slot));
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
@@ -162,7 +203,7 @@ __device__ __forceinline__ int finish_deferred(float best, int bcol, uint32_t sl
 #pragma unroll
     for (int j = 6; j >= 0; --j)
         if (v[j] == best) i = j;
-    return best < CUDART_INF_F ? bcol + i : 0;       // no hit at all (every score NaN / +inf): index 0
+    return any_hit ? bcol + i : 0;       // no hit at all (every score NaN or at the initial bound): index 0
 }
 
 template <bool kNormSmem, int kEpiWarps, int kMode>
@@ -177,7 +218,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     const int num_nb = (K + BN - 1) / BN;
     float* smN = reinterpret_cast<float*>(smB + nstages * B_ST_BYTES);
     uint8_t* smP = reinterpret_cast<uint8_t*>(smN) + (kNormSmem ? num_nb * BN * 4 : 0);   // kMode 2: parked groups
-    Ctl* ctl = reinterpret_cast<Ctl*>(smP + (kMode == 2 ? 2 * kEpiWarps * 32 * 16 : 0));
+    uint8_t* smO = smP + (kMode >= 2 ? 2 * kEpiWarps * 32 * 16 : 0);     // kMode 3: constant [128 x 16] "ones" operand (4 KiB)
+    Ctl* ctl = reinterpret_cast<Ctl*>(smO + (kMode == 3 ? 4096 : 0));
+    const uint8_t* aug_img = reinterpret_cast<const uint8_t*>(norms + num_nb * BN);   // behind the K_pad norms
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -207,6 +250,14 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         float4* dst = reinterpret_cast<float4*>(smN);
         for (int i = threadIdx.x - 128; i < num_nb * (BN / 4); i += kEpiWarps * 32) dst[i] = __ldg(src + i);
     }
+    if (kMode == 3 && threadIdx.x >= 128 && threadIdx.x < 256) {
+        // A-side partner of the aug image: every row is (1, 1, 1, 0, ..., 0), canonical no-swizzle K-major layout
+        const int r = threadIdx.x - 128;
+        uint8_t* p = smO + (r >> 3) * 256 + (r & 7) * 16;
+        *reinterpret_cast<uint4*>(p) = make_uint4(0x3F803F80u, 0x00003F80u, 0u, 0u);
+        *reinterpret_cast<uint4*>(p + 128) = make_uint4(0u, 0u, 0u, 0u);
+        fence_proxy_async();               // generic-proxy writes -> visible to the tensor core's async proxy
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -226,7 +277,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                                      (int)(tile * BM), kEvictFirst);
             };
             uint32_t st = 0, ph = 0, j = 0;
-            const int loads_per_slab = num_nb * nkb;
+            const int loads_per_slab = num_nb * (nkb + (kMode == 3 ? 1 : 0));
             const int trigger = loads_per_slab < nstages ? loads_per_slab : nstages;
             if (nabuf == 2 && (int64_t)blockIdx.x < ntiles) load_a(0, blockIdx.x);
             for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++j) {
@@ -242,6 +293,13 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                         // next slab's rows: requested once this slab's first ring-full of codebook stages is in
                         // flight, i.e. about when the previous slab retires and frees the other A buffer
+                        if (++issued == trigger && nabuf == 2 && next < ntiles) load_a(j + 1, next);
+                    }
+                    if (kMode == 3) {       // one more ring stage per tile: the 8 KiB aug block of these 256 codes
+                        mbar_wait(&ctl->b_empty[st], ph ^ 1, 2);
+                        mbar_arrive_expect_tx(&ctl->b_full[st], 8192);
+                        bulk_load_1d(smB + st * B_ST_BYTES, aug_img + (size_t)nb * 8192, 8192, &ctl->b_full[st]);
+                        if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                         if (++issued == trigger && nabuf == 2 && next < ntiles) load_a(j + 1, next);
                     }
                 }
@@ -277,6 +335,14 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                         umma_commit(&ctl->b_empty[st]);        // stage reusable once these MMAs retire
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                     }
+                    if (kMode == 3) {       // + [1,1,1,0..] x [h1,h2,h3,0..]^T = -||e||^2/2 into the same accumulator
+                        mbar_wait(&ctl->b_full[st], ph, 5);
+                        tc_fence_after();
+                        umma_bf16_ss(d_tmem, make_sdesc_none(smem_u32(smO), 128, 256),
+                                     make_sdesc_none(b_addr + st * B_ST_BYTES, 128, 256), idesc, 1u);
+                        umma_commit(&ctl->b_empty[st]);
+                        if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
+                    }
                     umma_commit(&ctl->t_full[acc]);            // accumulator tile complete
                 }
                 umma_commit(&ctl->a_empty[buf]);               // slab of z no longer read
@@ -294,7 +360,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         constexpr uint32_t slot_stride = kEpiWarps * 32 * 16;
         uint32_t it = 0, xb = 0;
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, xb ^= 1) {
-            float best = CUDART_INF_F;
+            float best = kMode == 3 ? -CUDART_INF_F : CUDART_INF_F;      // kMode 3 tracks a maximum
             int bi = 0;
             for (int nb = 0; nb < num_nb; ++nb, ++it) {
                 const uint32_t acc = it & 1, acc_ph = (it >> 1) & 1;
@@ -313,9 +379,11 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                 tmem_ld_32x32b_x32(taddr + 32, rb);
                 tmem_wait_ld();
                 if (CW == 128) {
-                    fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0, best, bi, slot, slot_stride, dbg);
+                    if (kMode == 3) fold_chunk_aug(ra, col0, best, bi, slot, slot_stride);
+                    else fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0, best, bi, slot, slot_stride, dbg);
                     tmem_ld_32x32b_x32(taddr + 64, ra);          // in flight while the second chunk is folded
-                    fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + 32, best, bi, slot, slot_stride, dbg);
+                    if (kMode == 3) fold_chunk_aug(rb, col0 + 32, best, bi, slot, slot_stride);
+                    else fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + 32, best, bi, slot, slot_stride, dbg);
                     tmem_ld_32x32b_x32(taddr + 96, rb);
                     tmem_wait_ld();
                 }
@@ -327,10 +395,16 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     bi += (int)(ra[0] ^ rb[5] ^ ra[31] ^ rb[17]);
                     continue;
                 }
-                fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0 + CW - 64, best, bi, slot, slot_stride, dbg);
-                fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + CW - 32, best, bi, slot, slot_stride, dbg);
+                if (kMode == 3) fold_chunk_aug(ra, col0 + CW - 64, best, bi, slot, slot_stride);
+                    else fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0 + CW - 64, best, bi, slot, slot_stride, dbg);
+                if (kMode == 3) fold_chunk_aug(rb, col0 + CW - 32, best, bi, slot, slot_stride);
+                    else fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + CW - 32, best, bi, slot, slot_stride, dbg);
             }
-            if (kMode == 2) bi = finish_deferred(best, bi, slot, slot_stride);
+            if (kMode == 2) bi = finish_deferred(best, bi, slot, slot_stride, best < CUDART_INF_F);
+            if (kMode == 3) {
+                bi = finish_deferred(best, bi, slot, slot_stride, best > -CUDART_INF_F);
+                best = -2.f * best;           // back to the score scale ||e||^2 - 2 z.e (exact, order-reversing)
+            }
             const int rl = q * 32 + lane;
             if (part != 0) {
                 ctl->xbest[xb][part][rl] = best;
@@ -412,20 +486,47 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
                "vq_assign(bf16): z and E_bf16 must be 16-byte aligned");
     const int nkb = (D + BK - 1) / BK;
     const int num_nb = (K + BN - 1) / BN;
-    // shared-memory plan: [A slab x nabuf][codebook ring x nstages][||e||^2 (optional)][Ctl]
+    static int epi_warps = 0, dbg = 0, mode_override = -1;
+    if (epi_warps == 0) {
+        const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // tuning knob: 8 or 16 epilogue warps
+        epi_warps = (ev != nullptr && atoi(ev) == 8) ? 8 : 16;
+        ev = getenv("VQ_ASSIGN_DBG");                            // 1/2/3: timing experiments, results are WRONG
+        if (ev != nullptr) dbg = atoi(ev);
+        ev = getenv("VQ_ASSIGN_MODE");                           // force an epilogue mode (0..3)
+        if (ev != nullptr) mode_override = atoi(ev);
+    }
+    // Epilogue mode (see fold_chunk / fold_chunk_aug).  The epilogue, not the tensor pipe, bounds this kernel when
+    // D is small (a 128 x 256 tile costs D/16 MMAs but always 32768 compare-selects), so:
+    //   D <= 128          mode 3: ||e||^2 rides through the tensor core as one more K step, arg-max of the raw accumulator,
+    //                     winning group parked in shared memory
+    //   D > 128, K < 4096 mode 2: FFMA2 scores, winning group parked
+    //   D > 128, K >=4096 mode 1: FFMA2 scores, immediate search inside the group of 8
+    //   measured on B200 (C2: K=1024 D=128): mode 0 0.365 ms, 1 0.386, 2 0.347; (C4: K=8192 D=256): mode 0 1.53 ms, 1 1.52
+    int mode = D <= 128 ? 3 : (K >= 4096 ? 1 : 2);
+    if (mode_override >= 0 && mode_override <= 3) mode = mode_override;
+    // shared-memory plan: [A slab x nabuf][codebook ring x nstages][||e||^2 (modes 0-2, optional)][parked groups
+    // (modes 2, 3)][ones operand (mode 3)][Ctl]
     //   norms go to shared memory when K <= 8192 and that still leaves >= 3 ring stages;
     //   the slab is double-buffered when that still leaves >= 4 ring stages.
-    const int avail = SMEM_LIMIT - 1024 - (int)sizeof(Ctl);
+    const int park_bytes = 2 * epi_warps * 32 * 16;
     const int a_bytes = nkb * A_KB_BYTES;
     const int norm_bytes = num_nb * BN * 4;
-    bool norm_smem = K <= NORM_SMEM_MAX && (avail - a_bytes - norm_bytes) / B_ST_BYTES >= 3;
-    const int after_norm = avail - (norm_smem ? norm_bytes : 0);
-    const int nabuf = (after_norm - 2 * a_bytes) / B_ST_BYTES >= 4 ? 2 : 1;
-    int nstages = (after_norm - nabuf * a_bytes) / B_ST_BYTES;
-    if (nstages > 6) nstages = 6;
+    int avail = 0, nabuf = 1, nstages = 0, extra = 0;
+    bool norm_smem = false;
+    for (;;) {
+        extra = (mode >= 2 ? park_bytes : 0) + (mode == 3 ? 4096 : 0);
+        avail = SMEM_LIMIT - 1024 - (int)sizeof(Ctl) - extra;
+        norm_smem = mode != 3 && K <= NORM_SMEM_MAX && (avail - a_bytes - norm_bytes) / B_ST_BYTES >= 3;
+        const int after_norm = avail - (norm_smem ? norm_bytes : 0);
+        nabuf = (after_norm - 2 * a_bytes) / B_ST_BYTES >= 4 ? 2 : 1;
+        nstages = (after_norm - nabuf * a_bytes) / B_ST_BYTES;
+        if (nstages > 6) nstages = 6;
+        if (nstages >= 3 || mode == 0) break;
+        mode = mode == 3 ? 2 : 0;                      // not enough room for the ring: fall back to a leaner mode
+    }
     VQ_REQUIRE(nstages >= 2, "vq_assign(bf16): D=%d leaves no room for the codebook ring", D);
-    const size_t smem_bytes = 1024 + (size_t)nabuf * a_bytes + (size_t)nstages * B_ST_BYTES +
-                              (norm_smem ? norm_bytes : 0) + sizeof(Ctl);
+    const size_t smem_total = 1024 + (size_t)nabuf * a_bytes + (size_t)nstages * B_ST_BYTES +
+                              (norm_smem ? norm_bytes : 0) + extra + sizeof(Ctl);
 
     CUtensorMap tm_z, tm_e;
     int rc = make_tmap(&tm_z, z_bf16, N, D, ldz, BM);
@@ -433,30 +534,12 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     rc = make_tmap(&tm_e, E_bf16, K, D, D, BN);
     if (rc != VQ_OK) return rc;
 
-    static int epi_warps = 0, dbg = 0;
-    if (epi_warps == 0) {
-        const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // tuning knob: 8 or 16 epilogue warps
-        epi_warps = (ev != nullptr && atoi(ev) == 8) ? 8 : 16;
-        ev = getenv("VQ_ASSIGN_DBG");                            // 1/2: timing experiments, results are WRONG
-        if (ev != nullptr) dbg = atoi(ev);
-    }
     const int64_t ntiles = (N + BM - 1) / BM;
     const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
     void (*kern)(const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int, int32_t*, float*, int);
-    // what happens when a chunk holds a new minimum (see fold_chunk): large K -> search inside the group of 8 at once;
-    // small K -> park the group in shared memory and search once per slab (needs 16 KiB of shared memory).
-    //   measured on B200: C4 (K=8192) mode 1 1.52 ms vs mode 0 1.53 ms; C2 (K=1024) mode 0 0.365 ms, mode 1 0.386 ms
-    static int mode_override = -1;
-    {
-        const char* ev = getenv("VQ_ASSIGN_MODE");
-        if (ev != nullptr) mode_override = atoi(ev);
-    }
-    int mode = K >= 4096 ? 1 : 2;
-    if (mode_override >= 0 && mode_override <= 2) mode = mode_override;
-    const size_t park_bytes = (size_t)2 * epi_warps * 32 * 16;
-    if (mode == 2 && smem_bytes + park_bytes > (size_t)SMEM_LIMIT) mode = 0;
-    const size_t smem_total = smem_bytes + (mode == 2 ? park_bytes : 0);
-#define VQ_PICK(NS, EW) (mode == 2 ? assign_tc_kernel<NS, EW, 2> : mode == 1 ? assign_tc_kernel<NS, EW, 1> : assign_tc_kernel<NS, EW, 0>)
+#define VQ_PICK(NS, EW)                                                                    \
+    (mode == 3 ? assign_tc_kernel<false, EW, 3> : mode == 2 ? assign_tc_kernel<NS, EW, 2> \
+                                              : mode == 1 ? assign_tc_kernel<NS, EW, 1> : assign_tc_kernel<NS, EW, 0>)
     if (norm_smem) kern = epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
     else kern = epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
 #undef VQ_PICK

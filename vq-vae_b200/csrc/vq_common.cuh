@@ -147,6 +147,13 @@ __device__ __forceinline__ void tma_load_2d_hint(void* smem_dst, const CUtensorM
         "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
         : "memory");
 }
+// 1-D bulk copy global -> shared, completion on an mbarrier (bytes and addresses multiples of 16)
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 // L2 eviction policies (createpolicy encodings used by CUTLASS' TMA::CacheHintSm90)
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast  = 0x14F0000000000000ull;
@@ -196,6 +203,14 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
 __device__ __forceinline__ uint64_t make_sdesc_sw128(uint32_t smem_addr) {
     return static_cast<uint64_t>((smem_addr >> 4) & 0x3FFFu) | (static_cast<uint64_t>(1024 >> 4) << 32) |
            (1ull << 46) | (2ull << 61);
+}
+
+// Shared-memory matrix descriptor, K-major operand WITHOUT swizzle (canonical "interleave" layout, cute
+// ((8,m),(T,2)):((1T,SBO),(1,LBO))): a core matrix is 8 rows x 16 bytes stored contiguously (128 B); lbo = byte distance
+// between the two 16-byte K halves of a UMMA K step, sbo = byte distance between consecutive groups of 8 rows.
+__device__ __forceinline__ uint64_t make_sdesc_none(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+    return static_cast<uint64_t>((smem_addr >> 4) & 0x3FFFu) | (static_cast<uint64_t>((lbo >> 4) & 0x3FFFu) << 16) |
+           (static_cast<uint64_t>((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
 }
 
 // TMEM -> registers: lane i of the warp reads TMEM lane (base_lane + i), 32 consecutive fp32 columns.

@@ -83,6 +83,29 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
     }
 }
 
+// "aug" image behind the K_pad norms (float offset K_pad): per 256-code tile an 8 KiB block holding -||e_k||^2 / 2 split
+// into three bf16 pieces (h1 + h2 + h3 reproduces the fp32 value), laid out as the canonical no-swizzle K-major UMMA
+// operand [256 codes x 16] (core matrix = 8 rows x 16 B; group of 8 rows g at g*256, second K half at +128).  The
+// tensor-core search multiplies it by a constant [1,1,1,0..] block so the accumulator already holds z.e - ||e||^2/2.
+__device__ __forceinline__ void write_aug(float* e_norm2, int norm_elems, int k, float nrm, bool pad) {
+    uint8_t* img = reinterpret_cast<uint8_t*>(e_norm2 + norm_elems) + (size_t)(k >> 8) * 8192 + ((k & 255) >> 3) * 256 +
+                   (k & 7) * 16;
+    uint4 lo = make_uint4(0u, 0u, 0u, 0u);
+    if (pad) {
+        lo.x = 0xFF80u;                                    // bf16 -inf: a padding code never wins the arg-max
+    } else {
+        const float h = -0.5f * nrm;
+        const __nv_bfloat16 h1 = __float2bfloat16_rn(h);
+        const float r1 = h - __bfloat162float(h1);
+        const __nv_bfloat16 h2 = __float2bfloat16_rn(r1);
+        const __nv_bfloat16 h3 = __float2bfloat16_rn(r1 - __bfloat162float(h2));
+        lo.x = (uint32_t)__bfloat16_as_ushort(h1) | ((uint32_t)__bfloat16_as_ushort(h2) << 16);
+        lo.y = (uint32_t)__bfloat16_as_ushort(h3);
+    }
+    *reinterpret_cast<uint4*>(img) = lo;
+    *reinterpret_cast<uint4*>(img + 128) = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // one warp per code row.  do_ema: decay step + Laplace-normalised codebook row; always: refresh bf16 shadow + norm.
 __global__ void __launch_bounds__(256)
 ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __restrict__ ema_sum,
@@ -93,7 +116,10 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (k >= norm_elems) return;
     if (k >= K) {
-        if (lane == 0) e_norm2[k] = CUDART_INF_F;
+        if (lane == 0) {
+            e_norm2[k] = CUDART_INF_F;
+            write_aug(e_norm2, norm_elems, k, 0.f, true);
+        }
         return;
     }
     const float omg = 1.0f - decay;
@@ -123,7 +149,10 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
         nrm = fmaf(en, en, nrm);
     }
     nrm = warp_sum(nrm);
-    if (lane == 0) e_norm2[k] = nrm;
+    if (lane == 0) {
+        e_norm2[k] = nrm;
+        write_aug(e_norm2, norm_elems, k, nrm, false);
+    }
 }
 
 template <typename T>
@@ -172,7 +201,7 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
     } else {
         VQ_REQUIRE(!do_ema, "vq_ema_update: do_ema without code_cnt");
     }
-    const int ne = vq_norm_elems(K);
+    const int ne = round_up(K, 256);                 // codes incl. padding; vq_norm_elems(K) floats = ne norms + aug image
     const float k_eps = (float)((double)K * (double)eps);
     ema_apply_kernel<<<(ne + 7) / 8, 256, 0, st>>>(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, k_eps,
                                                    do_ema, search, scal, static_cast<__nv_bfloat16*>(E_bf16), e_norm2,
