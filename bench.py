@@ -273,7 +273,7 @@ def run_native(args, wl):
         idx = torch.empty(N, dtype=torch.int32, device=dev)
         q = torch.empty_like(z)
         sq = torch.empty(1, device=dev)
-        stats = mod._stats_buffer()
+        stats = torch.empty(K * D + K, dtype=torch.float32, device=dev)   # private: never the module's exchange buffer
         csum, ccnt = stats[:K * D].view(K, D), stats[K * D:]
         Ec = mod.codebook.detach()
         flush = lambda: flush_buf.fill_(1)

@@ -96,6 +96,26 @@ int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* cod
                   int64_t* usage_total, int32_t* steps_since_used, float* perplexity /* [1] */,
                   int32_t* n_dead /* [1] */, int dead_after, int update_usage, void* ws, vq_stream_t stream);
 
+/* a-6 fused into a-7..a-9 (one process per GPU on one node): instead of all-reducing code_cnt / code_sum first, the
+ * update kernels read every rank's statistics buffer [code_sum (K*D) | code_cnt (K)] through peer memory (NVLink /
+ * NVSwitch) and add them in rank order, so every rank computes the bit-identical update.  peer_stats / peer_flags are
+ * HOST arrays of `world` DEVICE pointers (entry `rank` = this rank's own buffers, the others opened with vq_ipc_open);
+ * each flag array holds VQ_MAX_PEERS int32, zero-initialised; `epoch` must increase by one per call on every rank
+ * (start at 1).  The caller alternates between two statistics buffers from step to step (a rank may still be reading
+ * the previous step's buffer of a faster peer).  The reference has no distributed code: SURVEY.md 8(e). */
+#define VQ_MAX_PEERS 16
+#define VQ_IPC_HANDLE_BYTES 64
+int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D, float decay, float eps, int do_ema,
+                     int search, void* E_bf16, float* e_norm2, int64_t* usage_total, int32_t* steps_since_used,
+                     float* perplexity /* [1] */, int32_t* n_dead /* [1] */, int dead_after, int update_usage, void* ws,
+                     const void* const* peer_stats /* host [world] */, void* const* peer_flags /* host [world] */,
+                     int world, int rank, int epoch, vq_stream_t stream);
+/* CUDA IPC plumbing for the above: cudaMalloc + zero + export a 64-byte handle / open a peer's handle / release. */
+int vq_ipc_alloc(size_t bytes, void** dev_ptr /* host out */, void* handle_out /* host, 64 bytes */);
+int vq_ipc_free(void* dev_ptr);
+int vq_ipc_open(const void* handle /* host, 64 bytes */, void** dev_ptr /* host out */);
+int vq_ipc_close(void* dev_ptr);
+
 /* a-3/a-4 backward: grad_z = grad_q + (*grad_loss) * coef * (z - q), coef = 2*beta/(N*D) passed by the host.
  * grad_q may be NULL (no gradient arrived through the quantised output). */
 int vq_backward(const void* z, const void* q, const void* grad_q /* nullable */, int64_t N, int D, int64_t ldz,

@@ -33,8 +33,9 @@ def test_library_exports_every_declared_symbol():
 def test_host_only_entry_points():
     from vqvae_b200 import _lib
     lib = _lib.load(build_if_missing=True)
-    assert lib.vq_norm_elems(1) == 256 and lib.vq_norm_elems(256) == 256 and lib.vq_norm_elems(8192) == 8192
-    assert lib.vq_norm_elems(1000) == 1024
+    # K_pad norms + K_pad * 8 floats of operand image (include/vq_b200.h)
+    assert lib.vq_norm_elems(1) == 256 * 9 and lib.vq_norm_elems(256) == 256 * 9 and lib.vq_norm_elems(8192) == 8192 * 9
+    assert lib.vq_norm_elems(1000) == 1024 * 9
     out = ctypes.c_size_t(0)
     assert lib.vq_workspace_bytes(524288, 8192, 256, 0, ctypes.byref(out)) == 0
     small = out.value

@@ -17,6 +17,7 @@ VQ_DT_BF16, VQ_DT_F32 = 0, 1
 VQ_SEARCH_BF16, VQ_SEARCH_F32 = 0, 1
 VQ_STAT_SUM_Z, VQ_STAT_SUM_RESID = 0, 1
 ABI_VERSION = 1
+MAX_PEERS, IPC_HANDLE_BYTES = 16, 64
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 
@@ -35,6 +36,12 @@ SIGNATURES = {
     "vq_codebook_grad": (_i, [_p, _i, _i, _p, _f, _p, _p]),
     "vq_cast_bf16": (_i, [_p, _i64, _i, _i64, _p, _p]),
     "vq_layout_transpose": (_i, [_p, _p, _i64, _i64, _i64, _i, _p]),
+    "vq_ema_update_dp": (_i, [_p, _p, _p, _i, _i, _f, _f, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i, _p,
+                              C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _i, _i, _i, _p]),
+    "vq_ipc_alloc": (_i, [C.c_size_t, C.POINTER(C.c_void_p), _p]),
+    "vq_ipc_free": (_i, [_p]),
+    "vq_ipc_open": (_i, [_p, C.POINTER(C.c_void_p)]),
+    "vq_ipc_close": (_i, [_p]),
 }
 
 

@@ -3,6 +3,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstring>
 
 #include "vq_common.cuh"
 
@@ -35,7 +36,8 @@ int sm_count() {
 int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* code_cnt, const float* code_sum,
                       int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
                       int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
-                      int dead_after, int update_usage, void* ws, cudaStream_t st);
+                      int dead_after, int update_usage, void* ws, cudaStream_t st, const void* const* peer_stats,
+                      void* const* peer_flags, int world, int rank, int epoch);
 int launch_backward(const void* z, const void* q, const void* gq, int64_t N, int D, int64_t ldz,
                     const float* grad_loss, float coef, void* gz, int dtype, cudaStream_t st);
 int launch_codebook_grad(const float* resid, int K, int D, const float* grad_loss, float coef, float* gE,
@@ -67,7 +69,8 @@ int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf
     VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_prepare_codebook: bad search mode %d", search);
     VQ_REQUIRE(search != VQ_SEARCH_BF16 || E_bf16 != nullptr, "vq_prepare_codebook: E_bf16 required for VQ_SEARCH_BF16");
     return launch_ema_update(const_cast<float*>(E_f32), nullptr, nullptr, nullptr, nullptr, K, D, 0.f, 0.f, 0, search,
-                             E_bf16, e_norm2, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, stream);
+                             E_bf16, e_norm2, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, stream, nullptr, nullptr,
+                             0, 0, 0);
 }
 
 int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32, const void* E_bf16,
@@ -124,7 +127,53 @@ int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* cod
     VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_ema_update: bad search mode %d", search);
     return launch_ema_update(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, do_ema, search, E_bf16,
                              e_norm2, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws,
-                             stream);
+                             stream, nullptr, nullptr, 0, 0, 0);
+}
+
+int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D, float decay, float eps, int do_ema,
+                     int search, void* E_bf16, float* e_norm2, int64_t* usage_total, int32_t* steps_since_used,
+                     float* perplexity, int32_t* n_dead, int dead_after, int update_usage, void* ws,
+                     const void* const* peer_stats, void* const* peer_flags, int world, int rank, int epoch,
+                     vq_stream_t stream) {
+    VQ_REQUIRE(peer_stats != nullptr && peer_flags != nullptr, "vq_ema_update_dp: peer arrays are NULL");
+    VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_ema_update_dp: bad search mode %d", search);
+    return launch_ema_update(E_f32, ema_cnt, ema_sum, nullptr, nullptr, K, D, decay, eps, do_ema, search, E_bf16, e_norm2,
+                             usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws, stream,
+                             peer_stats, peer_flags, world, rank, epoch);
+}
+
+// ---- CUDA IPC plumbing for the peer exchange (one allocation per rank: [stats buffer 0 | stats buffer 1 | flags])
+int vq_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out) {
+    VQ_REQUIRE(dev_ptr != nullptr && handle_out != nullptr && bytes > 0, "vq_ipc_alloc: bad arguments");
+    void* p = nullptr;
+    VQ_CHECK_CUDA(cudaMalloc(&p, bytes));
+    VQ_CHECK_CUDA(cudaMemset(p, 0, bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        set_error("cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+        return VQ_ERR_CUDA;
+    }
+    static_assert(sizeof(cudaIpcMemHandle_t) == VQ_IPC_HANDLE_BYTES, "IPC handle size");
+    memcpy(handle_out, &h, sizeof(h));
+    *dev_ptr = p;
+    return VQ_OK;
+}
+int vq_ipc_free(void* dev_ptr) {
+    if (dev_ptr != nullptr) VQ_CHECK_CUDA(cudaFree(dev_ptr));
+    return VQ_OK;
+}
+int vq_ipc_open(const void* handle, void** dev_ptr) {
+    VQ_REQUIRE(handle != nullptr && dev_ptr != nullptr, "vq_ipc_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    VQ_CHECK_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return VQ_OK;
+}
+int vq_ipc_close(void* dev_ptr) {
+    if (dev_ptr != nullptr) VQ_CHECK_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+    return VQ_OK;
 }
 
 int vq_backward(const void* z, const void* q, const void* grad_q, int64_t N, int D, int64_t ldz,

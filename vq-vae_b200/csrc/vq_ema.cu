@@ -16,17 +16,72 @@ struct Scal {          // lives at offset 0 of the workspace
     float pad[3];
 };
 
+// ---- a-6 fused into a-7: peer-memory exchange ---------------------------------------------------------------
+// With one process per GPU every rank exposes its step statistics [code_sum (K*D) | code_cnt (K)] through CUDA IPC.
+// Instead of an NCCL all-reduce followed by the update, the update kernels READ every rank's buffer over
+// NVLink / NVSwitch and add them in rank order 0..W-1, so all ranks compute bit-identical codebooks and the small
+// message (0.5 MiB at K=1024, D=128) costs one flag exchange instead of a collective's launch + ring latency.
+struct Peers {
+    const float* stats[VQ_MAX_PEERS];   // rank r's statistics buffer of this step (own buffer included)
+    int32_t* flags[VQ_MAX_PEERS];       // rank r's flag array [VQ_MAX_PEERS]; slot s = last epoch signalled by rank s
+    int world, rank, epoch;
+};
+__device__ __forceinline__ float ld_peer(const float* p) {
+    float v;
+    asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+    int32_t v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Tell every rank that this rank's statistics of `epoch` are complete (they were written by earlier kernels of this
+// stream), then wait until every rank has said the same.  Bounded spin: a missing rank traps instead of hanging.
+__device__ __forceinline__ void peers_signal_and_wait(const Peers& P) {
+    const int t = threadIdx.x;
+    if (t < P.world) {
+        __threadfence_system();
+        st_release_sys(P.flags[t] + P.rank, P.epoch);
+        const int32_t* mine = P.flags[P.rank] + t;
+        const long long t0 = clock64();
+        while (ld_acquire_sys(mine) < P.epoch) {
+            if (clock64() - t0 > VQ_HANG_CYCLES) {
+                printf("vq_b200: rank %d timed out waiting for rank %d (epoch %d)\n", P.rank, t, P.epoch);
+                __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
 // one block.  tot_new = sum_k (g n_k + (1-g) cnt_k) in a fixed order (double); usage / dead / perplexity.
+// kPeer: code_cnt is the sum over ranks of the peers' counts (read over NVLink after the flag exchange); the reduced
+// counts are also written to cnt_red (local) for the second pass below and for ema_apply_kernel.
+template <bool kPeer>
 __global__ void __launch_bounds__(1024)
 ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ code_cnt, int K, float decay,
                   int do_ema, Scal* __restrict__ scal, int64_t* __restrict__ usage_total,
                   int32_t* __restrict__ steps_since_used, float* __restrict__ perplexity, int32_t* __restrict__ n_dead,
-                  int dead_after, int update_usage) {
+                  int dead_after, int update_usage, const Peers P, int64_t KD, float* __restrict__ cnt_red) {
     __shared__ double sh[3][32];
     const int t = threadIdx.x;
     const float omg = 1.0f - decay;
     double s_n = 0.0, s_c = 0.0;
     int dead = 0;
+    if (kPeer) {
+        peers_signal_and_wait(P);
+        for (int k = t; k < K; k += 1024) {
+            float c = 0.f;
+            for (int r = 0; r < P.world; ++r) c = __fadd_rn(c, ld_peer(P.stats[r] + KD + k));
+            cnt_red[k] = c;
+        }
+        __syncthreads();
+        code_cnt = cnt_red;
+    }
     for (int k = t; k < K; k += 1024) {
         const float c = code_cnt[k];
         if (do_ema) s_n += (double)__fadd_rn(__fmul_rn(decay, ema_cnt[k]), __fmul_rn(omg, c));
@@ -107,11 +162,13 @@ __device__ __forceinline__ void write_aug(float* e_norm2, int norm_elems, int k,
 }
 
 // one warp per code row.  do_ema: decay step + Laplace-normalised codebook row; always: refresh bf16 shadow + norm.
+// kPeer: the per-code sums are added over the ranks' buffers (peer loads) in rank order.
+template <bool kPeer>
 __global__ void __launch_bounds__(256)
 ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __restrict__ ema_sum,
                  const float* __restrict__ code_cnt, const float* __restrict__ code_sum, int K, int D, float decay,
                  float eps, float k_eps, int do_ema, int search, const Scal* __restrict__ scal,
-                 __nv_bfloat16* __restrict__ E_bf16, float* __restrict__ e_norm2, int norm_elems) {
+                 __nv_bfloat16* __restrict__ E_bf16, float* __restrict__ e_norm2, int norm_elems, const Peers P) {
     const int lane = threadIdx.x & 31;
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (k >= norm_elems) return;
@@ -136,7 +193,14 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
         const int64_t o = (int64_t)k * D + d;
         float ev;
         if (do_ema) {
-            const float m = __fadd_rn(__fmul_rn(decay, ema_sum[o]), __fmul_rn(omg, code_sum[o]));
+            float cs;
+            if (kPeer) {
+                cs = 0.f;
+                for (int r = 0; r < P.world; ++r) cs = __fadd_rn(cs, ld_peer(P.stats[r] + o));
+            } else {
+                cs = code_sum[o];
+            }
+            const float m = __fadd_rn(__fmul_rn(decay, ema_sum[o]), __fmul_rn(omg, cs));
             ema_sum[o] = m;
             ev = __fdiv_rn(m, nhat);
             E[o] = ev;
@@ -184,7 +248,23 @@ __global__ void codebook_grad_kernel(const float* __restrict__ resid, int64_t n,
 int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* code_cnt, const float* code_sum,
                       int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
                       int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
-                      int dead_after, int update_usage, void* ws, cudaStream_t st) {
+                      int dead_after, int update_usage, void* ws, cudaStream_t st, const void* const* peer_stats,
+                      void* const* peer_flags, int world, int rank, int epoch) {
+    Peers P;
+    P.world = 0; P.rank = 0; P.epoch = 0;
+    const bool peer = peer_stats != nullptr;
+    if (peer) {
+        VQ_REQUIRE(world >= 1 && world <= VQ_MAX_PEERS && rank >= 0 && rank < world && peer_flags != nullptr && epoch > 0,
+                   "vq_ema_update_dp: bad world=%d rank=%d epoch=%d (at most %d ranks)", world, rank, epoch, VQ_MAX_PEERS);
+        for (int r = 0; r < world; ++r) {
+            VQ_REQUIRE(peer_stats[r] != nullptr && peer_flags[r] != nullptr, "vq_ema_update_dp: NULL peer pointer %d", r);
+            P.stats[r] = static_cast<const float*>(peer_stats[r]);
+            P.flags[r] = static_cast<int32_t*>(peer_flags[r]);
+        }
+        P.world = world; P.rank = rank; P.epoch = epoch;
+        code_cnt = P.stats[rank] + (int64_t)K * D;          // non-NULL marker; the kernels read the peers' buffers
+        code_sum = P.stats[rank];
+    }
     VQ_REQUIRE(K > 0 && D > 0, "vq_ema_update: bad shape K=%d D=%d", K, D);
     VQ_REQUIRE(E_f32 != nullptr && e_norm2 != nullptr, "vq_ema_update: E_f32 and e_norm2 are required");
     Scal* scal = static_cast<Scal*>(ws);
@@ -194,8 +274,16 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                    "vq_ema_update: statistics buffers and workspace are required when code_cnt is given");
         VQ_REQUIRE(!do_ema || (ema_cnt != nullptr && ema_sum != nullptr && code_sum != nullptr),
                    "vq_ema_update: do_ema needs ema_cnt, ema_sum and code_sum");
-        ema_totals_kernel<<<1, 1024, 0, st>>>(ema_cnt, code_cnt, K, decay, do_ema, scal, usage_total, steps_since_used,
-                                              perplexity, n_dead, dead_after, update_usage);
+        float* cnt_red = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256);    // reserved by ws_layout
+        if (peer)
+            ema_totals_kernel<true><<<1, 1024, 0, st>>>(ema_cnt, code_cnt, K, decay, do_ema, scal, usage_total,
+                                                        steps_since_used, perplexity, n_dead, dead_after, update_usage,
+                                                        P, (int64_t)K * D, cnt_red);
+        else
+            ema_totals_kernel<false><<<1, 1024, 0, st>>>(ema_cnt, code_cnt, K, decay, do_ema, scal, usage_total,
+                                                         steps_since_used, perplexity, n_dead, dead_after, update_usage,
+                                                         P, 0, nullptr);
+        if (peer) code_cnt = cnt_red;
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
     } else {
@@ -203,9 +291,14 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
     }
     const int ne = round_up(K, 256);                 // codes incl. padding; vq_norm_elems(K) floats = ne norms + aug image
     const float k_eps = (float)((double)K * (double)eps);
-    ema_apply_kernel<<<(ne + 7) / 8, 256, 0, st>>>(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, k_eps,
-                                                   do_ema, search, scal, static_cast<__nv_bfloat16*>(E_bf16), e_norm2,
-                                                   ne);
+    if (peer && do_ema)
+        ema_apply_kernel<true><<<(ne + 7) / 8, 256, 0, st>>>(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps,
+                                                             k_eps, do_ema, search, scal,
+                                                             static_cast<__nv_bfloat16*>(E_bf16), e_norm2, ne, P);
+    else
+        ema_apply_kernel<false><<<(ne + 7) / 8, 256, 0, st>>>(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps,
+                                                              k_eps, do_ema, search, scal,
+                                                              static_cast<__nv_bfloat16*>(E_bf16), e_norm2, ne, P);
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

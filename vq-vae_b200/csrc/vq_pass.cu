@@ -59,34 +59,6 @@ __global__ void __launch_bounds__(512) hist_smem_kernel(const int32_t* __restric
     }
 }
 
-__global__ void __launch_bounds__(512) scatter_smem_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int R,
-                                                           int* __restrict__ cursor, int32_t* __restrict__ perm) {
-    extern __shared__ int sh[];
-    int* sh_cnt = sh;
-    int* sh_base = sh + K;
-    for (int k = threadIdx.x; k < K; k += blockDim.x) sh_cnt[k] = 0;
-    __syncthreads();
-    const int64_t a = (int64_t)blockIdx.x * R, b = min(N, a + R);
-    for (int64_t n = a + threadIdx.x; n < b; n += blockDim.x) {
-        int c = idx[n];
-        if ((unsigned)c >= (unsigned)K) c = 0;
-        atomicAdd(&sh_cnt[c], 1);
-    }
-    __syncthreads();
-    for (int k = threadIdx.x; k < K; k += blockDim.x) {
-        const int v = sh_cnt[k];
-        if (v != 0) sh_base[k] = atomicAdd(&cursor[k], v);      // claim a contiguous range of code k's segment
-        sh_cnt[k] = 0;
-    }
-    __syncthreads();
-    for (int64_t n = a + threadIdx.x; n < b; n += blockDim.x) {
-        int c = idx[n];
-        if ((unsigned)c >= (unsigned)K) c = 0;
-        const int r = atomicAdd(&sh_cnt[c], 1);
-        perm[sh_base[c] + r] = (int32_t)n;
-    }
-}
-
 // Fused variant used by the default path: every block first rebuilds the exclusive scan of the (complete) global
 // histogram in its own shared memory -- K counters, a few microseconds, in parallel on all blocks -- which removes
 // the single-block scan launch from the critical path; `cursor` starts at zero and holds the claimed count per code.
@@ -666,6 +638,7 @@ WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
     WsLayout L;
     size_t o = 0;
     L.scal = o;      o += 256;
+    o += al((size_t)K * 4);                               // offset 256: rank-reduced counts of vq_ema_update_dp
     L.zbf16 = o;     o += in_dtype == VQ_DT_F32 ? al((size_t)N * D * 2) : 0;
     L.cnt = o;       o += al((size_t)(2 * K + 4) * 4);     // [histogram K | cursor K | done counter]: one memset
     L.cursor = L.cnt + (size_t)K * 4;

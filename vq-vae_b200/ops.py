@@ -149,3 +149,22 @@ def layout_transpose(src: torch.Tensor, dst: torch.Tensor) -> None:
     B, R, C = src.shape
     assert src.is_contiguous() and dst.is_contiguous() and dst.shape == (B, C, R) and dst.dtype == src.dtype
     check(_lib.load().vq_layout_transpose(_ptr(src), _ptr(dst), B, R, C, _dt(src), _stream()), "vq_layout_transpose")
+
+
+def ema_update_dp(E: torch.Tensor, ema_cnt: torch.Tensor, ema_sum: torch.Tensor, decay: float, eps: float,
+                  do_ema: bool, search: str, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor,
+                  usage_total: torch.Tensor, steps_since_used: torch.Tensor, perplexity: torch.Tensor,
+                  n_dead: torch.Tensor, dead_after: int, update_usage: bool, ws: torch.Tensor, peer_stats, peer_flags,
+                  rank: int, epoch: int) -> None:
+    """a-6 fused into a-7..a-9: the update kernels add every rank's statistics through peer memory
+    (peer_stats / peer_flags: lists of `world` raw device pointers, own buffers at index `rank`)."""
+    _need_cuda(E, ema_cnt, ema_sum, E_bf16, e_norm2, usage_total, steps_since_used, perplexity, n_dead, ws)
+    K, D = E.shape
+    world = len(peer_stats)
+    ps = (C.c_void_p * world)(*[int(p) for p in peer_stats])
+    pf = (C.c_void_p * world)(*[int(p) for p in peer_flags])
+    check(_lib.load().vq_ema_update_dp(_ptr(E), _ptr(ema_cnt), _ptr(ema_sum), K, D, float(decay), float(eps),
+                                       int(bool(do_ema)), SEARCH_MODES[search], _ptr(E_bf16), _ptr(e_norm2),
+                                       _ptr(usage_total), _ptr(steps_since_used), _ptr(perplexity), _ptr(n_dead),
+                                       int(dead_after), int(bool(update_usage)), _ptr(ws), ps, pf, world, int(rank),
+                                       int(epoch), _stream()), "vq_ema_update_dp")

@@ -5,6 +5,7 @@ The reference has no distributed code (single GPU, frl/config/frl_training_v1.ya
 shard point north_star prescribes.  Backend-agnostic (NCCL on the GPUs, gloo in the CPU tests)."""
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -45,3 +46,85 @@ def assert_replicas_identical(codebook: torch.Tensor, group=None) -> None:
     for r, c in enumerate(allc):
         if not torch.equal(c, allc[0]):
             raise RuntimeError(f"codebook replica of rank {r} differs from rank 0")
+
+
+class _RawCudaBuffer:
+    """Exposes raw device memory to torch through __cuda_array_interface__ (no copy, no ownership)."""
+
+    def __init__(self, ptr: int, numel: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+class PeerExchange:
+    """Peer-memory statistics exchange for the fused a-6 + a-7 update (one process per GPU, one node).
+
+    Every rank owns ONE cudaMalloc'd allocation [stats 0 | stats 1 | flags] exported through CUDA IPC; the handles
+    travel once over the process group (all_gather_object), each rank maps its peers' allocations, and from then
+    on a step needs no collective call: the pass kernel writes the local statistics buffer of the step's parity,
+    vq_ema_update_dp signals / waits on the flags and reads all ranks' buffers over NVLink.
+    Two statistics buffers alternate because a slower rank may still be reading step t while a faster one already
+    writes step t+1 (the flag exchange of step t+1 orders everything older).
+    """
+
+    def __init__(self, numel: int, device: torch.device, group=None):
+        import ctypes as C
+        from . import _lib
+        lib = _lib.load()
+        self.group, self.numel, self.device = group, int(numel), device
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > _lib.MAX_PEERS:
+            raise RuntimeError(f"PeerExchange supports at most {_lib.MAX_PEERS} ranks")
+        stats_bytes = (self.numel * 4 + 255) // 256 * 256
+        self._stats_bytes = stats_bytes
+        total = 2 * stats_bytes + 256
+        base, handle = C.c_void_p(), C.create_string_buffer(_lib.IPC_HANDLE_BYTES)
+        _lib.check(lib.vq_ipc_alloc(total, C.byref(base), handle), "vq_ipc_alloc")
+        self._base, self._lib, self._opened = int(base.value), lib, []
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (os.getpid(), bytes(handle.raw)), group=group)
+        self._peer_base = []
+        for r, (pid, h) in enumerate(handles):
+            if r == self.rank:
+                self._peer_base.append(self._base)
+                continue
+            if pid == os.getpid():
+                raise RuntimeError("PeerExchange needs one process per GPU")
+            p = C.c_void_p()
+            _lib.check(lib.vq_ipc_open(C.create_string_buffer(h, _lib.IPC_HANDLE_BYTES), C.byref(p)), "vq_ipc_open")
+            self._opened.append(int(p.value))
+            self._peer_base.append(int(p.value))
+        self.stats = [torch.as_tensor(_RawCudaBuffer(self._base + i * stats_bytes, self.numel, "<f4"), device=device)
+                      for i in range(2)]
+        self.epoch = 0
+        dist.barrier(group=group)            # every allocation is zeroed and mapped before the first signal
+
+    def next_buffer(self) -> torch.Tensor:
+        """Statistics buffer the NEXT step writes (call once per step, before the pass kernel)."""
+        self.epoch += 1
+        return self.stats[self.epoch & 1]
+
+    def peer_stats(self):
+        return [b + (self.epoch & 1) * self._stats_bytes for b in self._peer_base]
+
+    def peer_flags(self):
+        return [b + 2 * self._stats_bytes for b in self._peer_base]
+
+    def close(self) -> None:
+        if self._lib is None:
+            return
+        torch.cuda.synchronize()
+        if dist.is_initialized():
+            dist.barrier(group=self.group)   # nobody still reads a buffer that is about to be freed
+        for p in self._opened:
+            self._lib.vq_ipc_close(p)
+        self._lib.vq_ipc_free(self._base)
+        self._lib, self.stats = None, []
+
+    def __del__(self):
+        try:
+            if self._lib is not None:
+                for p in self._opened:
+                    self._lib.vq_ipc_close(p)
+                self._lib.vq_ipc_free(self._base)
+        except Exception:
+            pass

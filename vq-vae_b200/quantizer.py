@@ -19,6 +19,7 @@ forward() on a CPU tensor raises: the kernels are sm_100a only and there is no f
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -28,6 +29,7 @@ from . import ops, parallel
 from ._lib import VQ_STAT_SUM_RESID, VQ_STAT_SUM_Z
 
 DEFAULT_DEAD_AFTER = 100
+PEER_ONE_SHOT_MAX_BYTES = 16 << 20      # total bytes a rank reads from its peers per step on the fused path
 
 
 class CodebookManager:
@@ -140,6 +142,9 @@ class VectorQuantizer(nn.Module):
     deterministic: code-sorted visiting order reproducible run to run (stable counting sort).
     channel_first: forward takes [B, D, *spatial] (the live model's layout, frl/models/representation.py:317-334)
         and returns quantized in the same layout, indices [B, *spatial]; one transpose pass each way (a-0).
+    peer_exchange: "auto" (default) uses the fused peer-memory exchange (parallel.PeerExchange + vq_ema_update_dp)
+        for the EMA statistics when the process group runs NCCL on one node, "nccl" always all-reduces with
+        torch.distributed, "peer" insists on the fused path.
     process_group / sync_stats: with torch.distributed initialised, per-code counts and sums are
         all-reduced (SUM) before the EMA step so every rank applies the identical update.
     """
@@ -147,7 +152,7 @@ class VectorQuantizer(nn.Module):
     def __init__(self, emb_dim: int, codebook_size: int, beta: float = 0.25, quantizer: str = "st",
                  ema_decay: float = 0.99, ema_eps: float = 1e-5, search: str = "auto",
                  dead_after: int = DEFAULT_DEAD_AFTER, deterministic: bool = False, process_group=None,
-                 sync_stats: bool = True, channel_first: bool = False):
+                 sync_stats: bool = True, channel_first: bool = False, peer_exchange: str = "auto"):
         super().__init__()
         if quantizer not in ("st", "ema"):
             raise ValueError(f"quantizer must be 'st' or 'ema', got {quantizer!r}")
@@ -159,6 +164,10 @@ class VectorQuantizer(nn.Module):
         self.search, self.dead_after, self.deterministic = search, int(dead_after), bool(deterministic)
         self.process_group, self.sync_stats = process_group, bool(sync_stats)
         self.channel_first = bool(channel_first)
+        if peer_exchange not in ("auto", "nccl", "peer"):
+            raise ValueError("peer_exchange must be 'auto', 'nccl' or 'peer'")
+        self.peer_exchange = peer_exchange
+        self._peers = None
         K, D = self.codebook_size, self.emb_dim
         init = torch.empty(K, D, dtype=torch.float32)
         if quantizer == "st":
@@ -252,9 +261,33 @@ class VectorQuantizer(nn.Module):
             self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
         return self._ws
 
+    def _use_peers(self) -> bool:
+        """Fused a-6 + a-7 path: EMA training step, NCCL group, every rank on this node."""
+        if self.peer_exchange == "nccl" or not (self.quantizer == "ema" and self.training and self._dist_active()):
+            return False
+        if self._peers is not None:
+            return True
+        import torch.distributed as dist
+        world = dist.get_world_size(self.process_group)
+        ok = dist.get_backend(self.process_group) == "nccl" and world <= int(os.environ.get("LOCAL_WORLD_SIZE", "1"))
+        if ok and self.peer_exchange == "auto":
+            # every rank reads all W buffers (one-shot): right for small statistics (latency-bound collective),
+            # wrong for large ones, where NCCL's bandwidth-optimal all-reduce moves 2 (W-1)/W of one buffer instead
+            ok = (self.codebook_size * (self.emb_dim + 1)) * 4 * world <= PEER_ONE_SHOT_MAX_BYTES
+        if not ok:
+            if self.peer_exchange == "peer":
+                raise RuntimeError("peer_exchange='peer' needs an NCCL process group whose ranks share one node")
+            self.peer_exchange = "nccl"
+            return False
+        K, D = self.codebook_size, self.emb_dim
+        self._peers = parallel.PeerExchange(K * D + K, self.codebook.device, self.process_group)
+        return True
+
     def _stats_buffer(self) -> torch.Tensor:
         K, D = self.codebook_size, self.emb_dim
         dev = self.codebook.device
+        if self._use_peers():
+            return self._peers.next_buffer()
         if self._stats is None or self._stats.device != dev:
             self._stats = torch.empty(K * D + K, dtype=torch.float32, device=dev)   # [code_sum | code_cnt]
         return self._stats
@@ -265,6 +298,14 @@ class VectorQuantizer(nn.Module):
     # ------------------------------------------------------------------ a-6 .. a-9
     def _finish_step(self, code_cnt, code_sum, search: str, ws) -> None:
         ema = self.quantizer == "ema" and self.training
+        if ema and self._peers is not None and self._use_peers():
+            E = self.codebook.detach()
+            px = self._peers
+            ops.ema_update_dp(E, self.ema_cnt, self.ema_sum, self.ema_decay, self.ema_eps, True, search, self._E_bf16,
+                              self._e_norm2, self.usage_total, self.steps_since_used, self.last_perplexity, self.n_dead,
+                              self.dead_after, True, ws, px.peer_stats(), px.peer_flags(), px.rank, px.epoch)
+            self._shadow_key = (E.data_ptr(), E._version, search)
+            return
         if self._dist_active():
             if ema:      # one collective over the contiguous [sum | cnt] buffer
                 parallel.allreduce_code_stats(self._stats, self.process_group)
