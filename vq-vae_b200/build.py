@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 LIB = os.path.join(HERE, "libvq_b200.so")
 STAMP = os.path.join(HERE, "csrc", ".build_stamp")
-SOURCES = ["vq_abi.cu", "vq_assign_tc.cu", "vq_assign_simt.cu", "vq_pass.cu", "vq_ema.cu", "vq_layout.cu"]
+SOURCES = ["vq_abi.cu", "vq_assign_tc.cu", "vq_assign_simt.cu", "vq_pass.cu", "vq_ema.cu", "vq_layout.cu", "vq_knn.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-shared", "-Xptxas", "-v", "-cudart", "static"]
 

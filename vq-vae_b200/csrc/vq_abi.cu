@@ -142,6 +142,15 @@ int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D,
                              peer_stats, peer_flags, world, rank, epoch);
 }
 
+int vq_knn_topk(const float* X, int64_t N, int C, const float* coords, const int32_t* patch, float pos_min_spatial, int k,
+                int64_t* knn_idx, float* knn_d2, void* ws, vq_stream_t stream) {
+    return launch_knn_topk(X, N, C, coords, patch, pos_min_spatial, k, knn_idx, knn_d2, ws, stream);
+}
+int vq_knn_mutual_pairs(const int64_t* knn_idx, int64_t N, int k, int64_t* pairs, int64_t* n_pairs, void* ws,
+                        vq_stream_t stream) {
+    return launch_knn_mutual(knn_idx, N, k, pairs, n_pairs, ws, stream);
+}
+
 // ---- CUDA IPC plumbing for the peer exchange (one allocation per rank: [stats buffer 0 | stats buffer 1 | flags])
 int vq_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out) {
     VQ_REQUIRE(dev_ptr != nullptr && handle_out != nullptr && bytes > 0, "vq_ipc_alloc: bad arguments");
