@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- quantised latent vectors / second for the VQ hot path (forward + EMA), BASELINE.json's metric.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c4|c1] [--impl native|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1|c2|c3|c4|c5] [--impl native|reference]
 
 One "step" = one pass of the hot path over one batch of synthetic latents: nearest-code search (a-1),
 fused gather / straight-through / loss / code statistics pass (a-2..a-5), code-stat all-reduce when N > 1
@@ -10,6 +10,8 @@ quantizer="ema".  Workloads:
     c2 (default, BASELINE configs[1]): N = 256*5*32*32 = 1 310 720 vectors/GPU, K=1024, D=128, bf16
     c4 (BASELINE configs[3])          : N = 524 288 vectors/GPU, K=8192, D=256, bf16
     c1 (BASELINE configs[0])          : N = 40 960, K=512, D=64 (the reference-scale case)
+    c3 (BASELINE configs[2])          : type/phase split, two codebooks K=2048 D=128 (262 144 + 1 310 720 vectors/GPU)
+    c5 (BASELINE configs[4])          : the batch-2048 step's quantiser load, 10 485 760 vectors/GPU, K=8192, D=256
 Weak scaling: every rank runs the same per-GPU workload on its own shard; `value` is the whole-job rate.
 Prints ONE JSON line on rank 0.
 """
@@ -32,7 +34,10 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {
     "c1": dict(N=8 * 5 * 32 * 32, K=512, D=64, desc="C1: 5x32x32 patch, batch 8, K=512 D=64"),
     "c2": dict(N=256 * 5 * 32 * 32, K=1024, D=128, desc="C2: batch 256 of 5x32x32 latents, K=1024 D=128, bf16 fwd+EMA"),
+    "c3": dict(N=256 * 5 * 32 * 32, N_type=256 * 32 * 32, K=2048, D=128,
+               desc="C3: type/phase split, two codebooks K=2048 D=128; type 262144 + phase 1310720 vectors per step"),
     "c4": dict(N=524288, K=8192, D=256, desc="C4: K=8192 D=256, 524288 vectors per GPU (4M per 8-GPU step)"),
+    "c5": dict(N=2048 * 5120, K=8192, D=256, desc="C5: quantiser load of the batch-2048 step, 10485760 vectors, K=8192 D=256"),
 }
 METRIC = "quantised latent vectors/sec (VQ fwd+EMA)"
 UNIT = "vectors/s"
@@ -207,6 +212,16 @@ def run_native(args, wl):
     with torch.no_grad():
         mod.codebook.copy_(E); mod.ema_sum.copy_(E)
     mod.train()
+    n_type = wl.get("N_type", 0)           # C3: a second codebook for the type stream, run underneath the phase stream
+    split = None
+    if n_type:
+        from vqvae_b200 import SplitQuantizer
+        split = SplitQuantizer(D, D, K, channel_first=False, beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5).to(dev)
+        split.quant_phase = mod
+        with torch.no_grad():
+            split.quant_type.codebook.copy_(E.flip(0)); split.quant_type.ema_sum.copy_(E.flip(0))
+        split.train()
+        z_type = z[:n_type].clone()
     peaks = load_peaks()
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
@@ -217,7 +232,7 @@ def run_native(args, wl):
 
     def step_resident():
         with torch.no_grad():
-            return mod(z)
+            return split(z_type, z) if split is not None else mod(z)
 
     # ---------------- value: inputs resident in HBM (335 MB of latents per step at c2 -- larger than L2)
     for _ in range(args.warmup):
@@ -242,10 +257,18 @@ def run_native(args, wl):
     z_dev = torch.empty_like(z)
     res_host = torch.empty(2, dtype=torch.float32).pin_memory()
 
+    if split is not None:
+        zt_host, zt_dev = z_type.cpu().pin_memory(), torch.empty_like(z_type)
+
     def step_e2e():
         z_dev.copy_(z_host, non_blocking=True)
         with torch.no_grad():
-            q, loss, idx = mod(z_dev)
+            if split is not None:
+                zt_dev.copy_(zt_host, non_blocking=True)
+                split(zt_dev, z_dev)
+                loss = split.loss
+            else:
+                q, loss, idx = mod(z_dev)
         res_host[0:1].copy_(loss.reshape(1), non_blocking=True)
         res_host[1:2].copy_(mod.last_perplexity, non_blocking=True)
         torch.cuda.current_stream().synchronize()             # the caller reads the step's result
@@ -303,13 +326,13 @@ def run_native(args, wl):
         dist.destroy_process_group()
     if rank != 0:
         return
-    n_total = N * world
+    n_total = (N + n_type) * world
     line = {"metric": METRIC, "value": n_total * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": wl["desc"], "N_per_gpu": N, "K": K, "D": D, "quantizer": "ema",
+            "config": {"workload": wl["desc"], "N_per_gpu": N + n_type, "K": K, "D": D, "quantizer": "ema",
                        "parallelism": f"dp{world}", "l2": "inputs larger than L2 (%.0f MB of latents per step)" % (N * D * 2 / 1e6)},
-            "e2e": {"value": n_total * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": N * D * 2,
+            "e2e": {"value": n_total * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (N + n_type) * D * 2,
                     "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": int(launches), "clocks": clk}
     line.update(line_extra)

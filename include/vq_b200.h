@@ -137,11 +137,12 @@ int vq_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_
  * fused distance + argmin search.  X [N, C] fp32 dense; coords [N, 2] fp32 and patch [N] int32 (both or neither) give the
  * within-patch spatial mask |coord_i - coord_j| < pos_min_spatial; k <= 32.  knn_idx [N, k] int64: the k nearest
  * (ascending squared distance, ties lower index first), -1 where fewer than k candidates survive the masks; knn_d2
- * (nullable) the squared distances.  ws: at least max(N, 1) * 4 bytes. */
+ * (nullable) the squared distances.  ws: vq_knn_workspace_bytes(N, C) bytes, 256-byte aligned (scratch for both calls). */
+int vq_knn_workspace_bytes(int64_t N, int C, size_t* out_bytes);
 int vq_knn_topk(const float* X, int64_t N, int C, const float* coords, const int32_t* patch, float pos_min_spatial, int k,
                 int64_t* knn_idx, float* knn_d2 /* nullable */, void* ws, vq_stream_t stream);
 /* pairs [N*k, 2] int64 receives every (i, j) with j in knn[i] and i in knn[j], ordered by i then by the rank of j;
- * n_pairs (device, [1] int64) the number written.  ws: at least max(N, 1) * 4 bytes. */
+ * n_pairs (device, [1] int64) the number written.  pairs 16-byte aligned; ws as above (any C). */
 int vq_knn_mutual_pairs(const int64_t* knn_idx, int64_t N, int k, int64_t* pairs, int64_t* n_pairs, void* ws,
                         vq_stream_t stream);
 

@@ -90,3 +90,37 @@ def test_cuda_topk_against_numpy_at_training_scale():
     pairs = knn.mutual_pairs(torch.from_numpy(got).cuda()).cpu().numpy()
     ref_pairs = KR.mutual_pairs(got)
     assert pairs.shape == ref_pairs.shape and (pairs == ref_pairs).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,C,k,masked", [(1000, 64, 16, True), (777, 36, 5, False), (4096, 128, 32, True), (300, 8, 16, True)])
+def test_cuda_tiled_path_equals_streaming_path(N, C, k, masked, monkeypatch):
+    """The tiled two-pass selection and the streaming sorted-list kernel share their arithmetic: results are bit-equal."""
+    from vqvae_b200 import knn
+    g = torch.Generator().manual_seed(N + C)
+    X = torch.randn(N, C, generator=g).cuda()
+    coords = torch.randint(0, 32, (N, 2), generator=g).float().cuda() if masked else None
+    patch = torch.randint(0, 4, (N,), generator=g).sort().values.int().cuda() if masked else None
+    a_idx, a_d = knn.knn_topk(X, k, coords, patch, 6.0, return_d2=True)
+    monkeypatch.setenv("VQ_KNN_PATH", "stream")
+    b_idx, b_d = knn.knn_topk(X, k, coords, patch, 6.0, return_d2=True)
+    assert torch.equal(a_idx, b_idx) and torch.equal(a_d, b_d)
+    ref, _ = KR.knn_topk(X.cpu().numpy(), k, None if coords is None else coords.cpu().numpy(),
+                         None if patch is None else patch.cpu().numpy(), 6.0)
+    assert (a_idx.cpu().numpy() != ref).mean() < 2e-3          # fp32 summation order: near-ties only
+
+
+@pytest.mark.gpu
+def test_cuda_masses_of_exact_ties_take_the_redo_path():
+    """Duplicated feature rows: hundreds of candidates at exactly the k-th distance overflow the survivor buffer; the
+    flagged rows are redone by the streaming kernel and the lowest indices win (torch.topk / stable argsort order)."""
+    from vqvae_b200 import knn
+    g = torch.Generator().manual_seed(5)
+    base = torch.randint(-3, 4, (3, 16), generator=g).float()   # small integers: every sum is exact in fp32, ties are exact
+    X = base[torch.arange(900) % 3].contiguous()                # 300 exact copies of each of 3 points
+    idx, d2 = knn.knn_topk(X.cuda(), 8, return_d2=True)
+    ref, vals = KR.knn_topk(X.numpy(), 8)
+    assert np.array_equal(idx.cpu().numpy(), ref)
+    assert float(d2.max()) == 0.0
+    pairs = knn.mutual_pairs(idx).cpu().numpy()
+    assert np.array_equal(pairs, KR.mutual_pairs(ref))

@@ -5,6 +5,6 @@ root forwards here).  Only what the hot path needs lives in this package: ``csrc
 ``_lib`` (ctypes binding), ``ops`` (tensor -> pointer wrappers) and ``quantizer`` (the nn.Module the
 reference scripts call).
 """
-from .quantizer import CodebookManager, VectorQuantizer, extract_code_usage_from_state  # noqa: F401
+from .quantizer import CodebookManager, SplitQuantizer, VectorQuantizer, extract_code_usage_from_state  # noqa: F401
 
-__all__ = ["VectorQuantizer", "CodebookManager", "extract_code_usage_from_state"]
+__all__ = ["VectorQuantizer", "SplitQuantizer", "CodebookManager", "extract_code_usage_from_state"]

@@ -42,6 +42,7 @@ SIGNATURES = {
     "vq_ipc_free": (_i, [_p]),
     "vq_ipc_open": (_i, [_p, C.POINTER(C.c_void_p)]),
     "vq_ipc_close": (_i, [_p]),
+    "vq_knn_workspace_bytes": (_i, [_i64, _i, C.POINTER(C.c_size_t)]),
     "vq_knn_topk": (_i, [_p, _i64, _i, _p, _p, _f, _i, _p, _p, _p, _p]),
     "vq_knn_mutual_pairs": (_i, [_p, _i64, _i, _p, _p, _p, _p]),
 }

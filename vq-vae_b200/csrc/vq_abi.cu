@@ -142,6 +142,11 @@ int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D,
                              peer_stats, peer_flags, world, rank, epoch);
 }
 
+int vq_knn_workspace_bytes(int64_t N, int C, size_t* out_bytes) {
+    VQ_REQUIRE(out_bytes != nullptr && N >= 0 && C > 0, "vq_knn_workspace_bytes: bad arguments N=%lld C=%d", (long long)N, C);
+    *out_bytes = knn_workspace_bytes(N, C);
+    return VQ_OK;
+}
 int vq_knn_topk(const float* X, int64_t N, int C, const float* coords, const int32_t* patch, float pos_min_spatial, int k,
                 int64_t* knn_idx, float* knn_d2, void* ws, vq_stream_t stream) {
     return launch_knn_topk(X, N, C, coords, patch, pos_min_spatial, k, knn_idx, knn_d2, ws, stream);

@@ -7,6 +7,7 @@ then by the neighbour's rank.  `chunk_size` is accepted for compatibility and ig
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import List, Optional, Sequence
 
 import torch
@@ -16,19 +17,25 @@ from ._lib import check
 from .ops import _need_cuda, _ptr, _stream
 
 
+def _workspace(N: int, Cdim: int, device) -> torch.Tensor:
+    out = C.c_size_t(0)
+    check(_lib.load().vq_knn_workspace_bytes(int(N), int(Cdim), C.byref(out)), "vq_knn_workspace_bytes")
+    return torch.empty(max(int(out.value), 256), dtype=torch.uint8, device=device)
+
+
 def knn_topk(features: torch.Tensor, k: int, coords: Optional[torch.Tensor] = None,
              patch: Optional[torch.Tensor] = None, pos_min_spatial: float = 4.0, return_d2: bool = False):
     """[N, C] fp32 -> knn_idx [N, k] int64 (-1 = no valid neighbour) (+ squared distances)."""
     _need_cuda(features, coords, patch)
     X = features.detach().to(torch.float32).contiguous()
-    N, C = X.shape
+    N, Cdim = X.shape
     knn = torch.empty((N, k), dtype=torch.int64, device=X.device)
     d2 = torch.empty((N, k), dtype=torch.float32, device=X.device) if return_d2 else None
-    ws = torch.empty(max(N, 1), dtype=torch.int32, device=X.device)
+    ws = _workspace(N, Cdim, X.device)
     if coords is not None:
         coords = coords.detach().to(torch.float32).contiguous()
         patch = patch.to(torch.int32).contiguous()
-    check(_lib.load().vq_knn_topk(_ptr(X), N, C, _ptr(coords), _ptr(patch), float(pos_min_spatial), int(k), _ptr(knn),
+    check(_lib.load().vq_knn_topk(_ptr(X), N, Cdim, _ptr(coords), _ptr(patch), float(pos_min_spatial), int(k), _ptr(knn),
                                   _ptr(d2), _ptr(ws), _stream()), "vq_knn_topk")
     return (knn, d2) if return_d2 else knn
 
@@ -38,7 +45,7 @@ def mutual_pairs(knn: torch.Tensor) -> torch.Tensor:
     N, k = knn.shape
     pairs = torch.empty((max(N * k, 1), 2), dtype=torch.int64, device=knn.device)
     n = torch.zeros(1, dtype=torch.int64, device=knn.device)
-    ws = torch.empty(max(N, 1), dtype=torch.int32, device=knn.device)
+    ws = _workspace(N, 4, knn.device)
     check(_lib.load().vq_knn_mutual_pairs(_ptr(knn), N, k, _ptr(pairs), _ptr(n), _ptr(ws), _stream()),
           "vq_knn_mutual_pairs")
     return pairs[:int(n)]                     # the size is data dependent: one device -> host read, as in the reference

@@ -355,3 +355,47 @@ class VectorQuantizer(nn.Module):
             if qcf.dtype != in_dtype:
                 qcf = qcf.to(in_dtype)
             return qcf.reshape(B, D, *spatial), loss, idx.reshape(B, *spatial)
+
+
+class SplitQuantizer(nn.Module):
+    """Two codebooks for the live model's two latent streams (BASELINE config 3): a `type` codebook over
+    z_type [B, D_type, H, W] and a `phase` codebook over z_phase [B, D_phase, T, H, W] (attributes `quant_type`, `quant_phase`)
+    (frl/models/representation.py:60-72, :317-374; both channel-first).  The two quantisers share nothing, so the
+    type stream (T times fewer vectors) runs on a side CUDA stream underneath the phase stream's kernels.
+
+    forward(z_type, z_phase) -> ((q_type, loss_type, idx_type), (q_phase, loss_phase, idx_phase)); `loss` is the sum
+    the training step adds to its objective, `perplexity` a dict.
+    """
+
+    def __init__(self, type_dim: int, phase_dim: int, codebook_size: int, channel_first: bool = True,
+                 overlap: bool = True, **kw):
+        super().__init__()
+        self.quant_type = VectorQuantizer(type_dim, codebook_size, channel_first=channel_first, **kw)
+        self.quant_phase = VectorQuantizer(phase_dim, codebook_size, channel_first=channel_first, **kw)
+        self.overlap = bool(overlap)
+        self._side: Optional[torch.cuda.Stream] = None
+        self.loss: Optional[torch.Tensor] = None
+
+    @property
+    def perplexity(self) -> dict:
+        return {"type": self.quant_type.perplexity, "phase": self.quant_phase.perplexity}
+
+    def forward(self, z_type: torch.Tensor, z_phase: torch.Tensor):
+        if not (z_type.is_cuda and z_phase.is_cuda):
+            raise RuntimeError("SplitQuantizer.forward needs CUDA tensors (no CPU fallback)")
+        if not self.overlap:
+            out_t, out_p = self.quant_type(z_type), self.quant_phase(z_phase)
+        else:
+            cur = torch.cuda.current_stream(z_type.device)
+            if self._side is None or self._side.device != z_type.device:
+                self._side = torch.cuda.Stream(device=z_type.device)
+            self._side.wait_stream(cur)                      # z_type was produced on the caller's stream
+            with torch.cuda.stream(self._side):
+                out_t = self.quant_type(z_type)
+            out_p = self.quant_phase(z_phase)
+            cur.wait_stream(self._side)
+            for t in out_t:                                  # allocated on the side stream, consumed on the caller's
+                t.record_stream(cur)
+            z_type.record_stream(self._side)
+        self.loss = out_t[1] + out_p[1]
+        return out_t, out_p
