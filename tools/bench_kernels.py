@@ -15,7 +15,11 @@ peaks = load_peaks()
 flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 flush = lambda: flush_buf.fill_(1)
 for name in sys.argv[1:] or ["c2", "c4"]:
-    wl = WORKLOADS[name]
+    if name in WORKLOADS:
+        wl = WORKLOADS[name]
+    else:                                   # ad-hoc shape "N,K,D"
+        n_, k_, d_ = (int(x) for x in name.split(","))
+        wl = dict(N=n_, K=k_, D=d_, desc=name)
     N, K, D = wl["N"], wl["K"], wl["D"]
     z, E = make_inputs(wl, 0, dev)
     E = E.to(dev)

@@ -1,10 +1,9 @@
 #!/bin/bash
-# scratch trip: new tests, kNN timing, c3 bench line
-mkdir -p gpurun_out
+# scratch trip: pair (plain remote arrive) vs single on the named workloads, then the parity tests with pair on
+mkdir -p gpurun_out; rm -f gpurun_out/kern.log
+run() { echo "== $*" | tee -a gpurun_out/kern.log; env "$@" timeout 300 python tools/bench_kernels.py c2 c4 c1 c3 c5 2>&1 | grep -v "^vq_assign" | tail -n 5 | cut -c1-75 | tee -a gpurun_out/kern.log; }
+run VQ_ASSIGN_PAIR=1
+run VQ_ASSIGN_PAIR=0
+run VQ_ASSIGN_PAIR=1 VQ_ASSIGN_DBG=2
 timeout 900 python -m pytest tests -q -m gpu -x --timeout=300 > gpurun_out/tests.log 2>&1; echo "tests exit $?" >> gpurun_out/tests.log
-tail -n 12 gpurun_out/tests.log
-timeout 300 python tools/bench_knn.py > gpurun_out/knn_bench.log 2>&1; echo "knn exit $?" >> gpurun_out/knn_bench.log
-timeout 300 python tools/bench_knn.py --patches 32 --anchors 256 > gpurun_out/knn_bench_8k.log 2>&1
-timeout 300 python tools/bench_knn.py --patches 16 --anchors 256 --channels 128 > gpurun_out/knn_bench_c128.log 2>&1
-timeout 300 python bench.py --workload c3 --skip-cpu > gpurun_out/bench_c3.log 2>&1; echo "c3 exit $?" >> gpurun_out/bench_c3.log
-for f in knn_bench knn_bench_8k knn_bench_c128 bench_c3; do echo "== $f"; tail -n 3 gpurun_out/$f.log | cut -c1-1800; done
+tail -n 4 gpurun_out/tests.log

@@ -206,17 +206,23 @@ __device__ __forceinline__ int finish_deferred(float best, int bcol, uint32_t sl
     return any_hit ? bcol + i : 0;       // no hit at all (every score NaN or at the initial bound): index 0
 }
 
-template <bool kNormSmem, int kEpiWarps, int kMode>
+// kPair: the kernel runs as clusters of two CTAs on the two SMs of a TPC and every MMA is a tcgen05 cta_group::2
+// instruction over a 256-row slab (128 rows per CTA) x 256 codes (128 codes of each stage in each CTA's shared memory,
+// see vq_common.cuh).  Per SM that halves the codebook bytes pulled from L2 (the binding resource of the single-CTA
+// kernel: 148 SMs x 64 B/clk against an L2 that delivers about 43 B/clk/SM) and the operand bytes read from shared memory.
+template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair>
 __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
-                 const float* __restrict__ norms, int64_t N, int K, int D, int nkb, int nstages, int nabuf,
-                 int32_t* __restrict__ idx, float* __restrict__ smin, int dbg) {
+                 const __grid_constant__ CUtensorMap tm_aug, const float* __restrict__ norms, int64_t N, int K, int D,
+                 int nkb, int nstages, int nabuf, int32_t* __restrict__ idx, float* __restrict__ smin, int dbg) {
+    constexpr int B_ROWS = kPair ? BN / 2 : BN;          // codes of a stage held by this CTA
+    constexpr int B_ST = B_ROWS * BK * 2;                // ring slot bytes (16 KiB / 32 KiB)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smA = smem;
     uint8_t* smB = smA + nabuf * nkb * A_KB_BYTES;
     const int num_nb = (K + BN - 1) / BN;
-    float* smN = reinterpret_cast<float*>(smB + nstages * B_ST_BYTES);
+    float* smN = reinterpret_cast<float*>(smB + nstages * B_ST);
     uint8_t* smP = reinterpret_cast<uint8_t*>(smN) + (kNormSmem ? num_nb * BN * 4 : 0);   // kMode 2: parked groups
     uint8_t* smO = smP + (kMode >= 2 ? 2 * kEpiWarps * 32 * 16 : 0);     // kMode 3: constant [128 x 16] "ones" operand (4 KiB)
     Ctl* ctl = reinterpret_cast<Ctl*>(smO + (kMode == 3 ? 4096 : 0));
@@ -224,19 +230,25 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int64_t ntiles = (N + BM - 1) / BM;
+    const uint32_t rank = kPair ? cluster_ctarank() : 0u;                 // 0 = leader (MMA issuer) of the pair
+    const int64_t unit = kPair ? (blockIdx.x >> 1) : blockIdx.x;          // slab-owning unit: a CTA or a CTA pair
+    const int64_t nunits = kPair ? (gridDim.x >> 1) : gridDim.x;
+    constexpr int SLAB = kPair ? 2 * BM : BM;                             // rows per slab of the unit
+    const int64_t ntiles = (N + SLAB - 1) / SLAB;
     const int a_bytes = nkb * A_KB_BYTES;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tm_z);
         prefetch_tmap(&tm_e);
+        if (kPair && kMode == 3) prefetch_tmap(&tm_aug);
     }
     if (warp == 1 && lane == 0) {
         for (int b = 0; b < 2; ++b) {
             mbar_init(&ctl->a_full[b], 1);
             mbar_init(&ctl->a_empty[b], 1);
             mbar_init(&ctl->t_full[b], 1);
-            mbar_init(&ctl->t_empty[b], kEpiWarps);
+            // pair: both CTAs' epilogues release it (dbg 4: timing experiment, the peer's epilogue stays silent)
+            mbar_init(&ctl->t_empty[b], (kPair && dbg != 4) ? 2 * kEpiWarps : kEpiWarps);
         }
         for (int s = 0; s < nstages; ++s) {
             mbar_init(&ctl->b_full[s], 1);
@@ -244,7 +256,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         }
         fence_mbar_init();
     }
-    if (warp == 2) tmem_alloc<TMEM_COLS>(&ctl->tmem_base);
+    if (warp == 2) {
+        if (kPair) tmem_alloc_pair<TMEM_COLS>(&ctl->tmem_base);
+        else tmem_alloc<TMEM_COLS>(&ctl->tmem_base);
+    }
     if (kNormSmem && warp >= 4) {          // ||e||^2 (padded with +inf to a multiple of BN) -> shared memory, once
         const float4* src = reinterpret_cast<const float4*>(norms);
         float4* dst = reinterpret_cast<float4*>(smN);
@@ -260,6 +275,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     }
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync_all();         // the peer's barriers are initialised before anything remote touches them
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
 
@@ -267,29 +283,42 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         // ------------------------------------------------------------------ TMA producer
         if (elect_one()) {
             // slab number j of this CTA lives in A buffer (j % nabuf); it is that buffer's (j / nabuf)-th use
+            // pair: loads land in THIS CTA's shared memory and complete on the LEADER's "full" barriers, which expect the
+            // bytes of both CTAs; each producer throttles on its own copy of the "empty" barriers (multicast commits)
+            const uint32_t lead_a_full = kPair ? map_to_cta(smem_u32(&ctl->a_full[0]), 0) : 0u;     // [buf]: + 8 * buf
+            const uint32_t lead_b_full = kPair ? map_to_cta(smem_u32(&ctl->b_full[0]), 0) : 0u;     // [st]:  + 8 * st
             auto load_a = [&](uint32_t j, int64_t tile) {
                 const uint32_t buf = nabuf == 2 ? (j & 1u) : 0u;
                 const uint32_t use = nabuf == 2 ? (j >> 1) : j;
                 mbar_wait(&ctl->a_empty[buf], (use & 1u) ^ 1u, 1);
-                mbar_arrive_expect_tx(&ctl->a_full[buf], a_bytes);
-                for (int kb = 0; kb < nkb; ++kb)
-                    tma_load_2d_hint(smA + buf * a_bytes + kb * A_KB_BYTES, &tm_z, &ctl->a_full[buf], kb * BK,
-                                     (int)(tile * BM), kEvictFirst);
+                if (rank == 0) mbar_arrive_expect_tx(&ctl->a_full[buf], kPair ? 2 * a_bytes : a_bytes);
+                const int row0 = (int)(tile * SLAB + rank * BM);
+                for (int kb = 0; kb < nkb; ++kb) {
+                    if (kPair)
+                        tma_load_2d_hint_pair(smA + buf * a_bytes + kb * A_KB_BYTES, &tm_z, lead_a_full + 8u * buf, kb * BK, row0,
+                                              kEvictFirst);
+                    else
+                        tma_load_2d_hint(smA + buf * a_bytes + kb * A_KB_BYTES, &tm_z, &ctl->a_full[buf], kb * BK, row0,
+                                         kEvictFirst);
+                }
             };
             uint32_t st = 0, ph = 0, j = 0;
             const int loads_per_slab = num_nb * (nkb + (kMode == 3 ? 1 : 0));
             const int trigger = loads_per_slab < nstages ? loads_per_slab : nstages;
-            if (nabuf == 2 && (int64_t)blockIdx.x < ntiles) load_a(0, blockIdx.x);
-            for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++j) {
+            if (nabuf == 2 && unit < ntiles) load_a(0, unit);
+            for (int64_t tile = unit; tile < ntiles; tile += nunits, ++j) {
                 if (nabuf == 1) load_a(j, tile);
-                const int64_t next = tile + gridDim.x;
+                const int64_t next = tile + nunits;
                 int issued = 0;
                 for (int nb = 0; nb < num_nb; ++nb) {
                     for (int kb = 0; kb < nkb; ++kb) {
                         mbar_wait(&ctl->b_empty[st], ph ^ 1, 2);
-                        mbar_arrive_expect_tx(&ctl->b_full[st], B_ST_BYTES);
-                        tma_load_2d_hint(smB + st * B_ST_BYTES, &tm_e, &ctl->b_full[st], kb * BK, nb * BN,
-                                         kEvictLast);
+                        if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[st], B_ST_BYTES);   // 32 KiB per stage either way
+                        if (kPair)
+                            tma_load_2d_hint_pair(smB + st * B_ST, &tm_e, lead_b_full + 8u * st, kb * BK,
+                                                  nb * BN + (int)rank * B_ROWS, kEvictLast);
+                        else
+                            tma_load_2d_hint(smB + st * B_ST, &tm_e, &ctl->b_full[st], kb * BK, nb * BN, kEvictLast);
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                         // next slab's rows: requested once this slab's first ring-full of codebook stages is in
                         // flight, i.e. about when the previous slab retires and frees the other A buffer
@@ -297,8 +326,12 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     }
                     if (kMode == 3) {       // one more ring stage per tile: the 8 KiB aug block of these 256 codes
                         mbar_wait(&ctl->b_empty[st], ph ^ 1, 2);
-                        mbar_arrive_expect_tx(&ctl->b_full[st], 8192);
-                        bulk_load_1d(smB + st * B_ST_BYTES, aug_img + (size_t)nb * 8192, 8192, &ctl->b_full[st]);
+                        if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[st], 8192);
+                        if (kPair)          // u64 view [K_pad / 64][256]: this CTA's 128 codes are 2 rows of 2 KiB
+                            tma_load_2d_hint_pair(smB + st * B_ST, &tm_aug, lead_b_full + 8u * st, 0,
+                                                  nb * 4 + (int)rank * 2, kEvictLast);
+                        else
+                            bulk_load_1d(smB + st * B_ST, aug_img + (size_t)nb * 8192, 8192, &ctl->b_full[st]);
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                         if (++issued == trigger && nabuf == 2 && next < ntiles) load_a(j + 1, next);
                     }
@@ -306,12 +339,20 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------------------------ MMA issuer
-        if (elect_one()) {
-            constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+        // ------------------------------------------------------------------ MMA issuer (pair: the leader CTA only)
+        if (rank == 0 && elect_one()) {
+            constexpr uint32_t idesc = make_idesc_bf16(kPair ? 2 * BM : BM, BN);
             const uint32_t a_addr = smem_u32(smA), b_addr = smem_u32(smB);
+            auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t acc_flag) {
+                if (kPair) umma_bf16_ss_pair(d, da, db, idesc, acc_flag);
+                else umma_bf16_ss(d, da, db, idesc, acc_flag);
+            };
+            auto commit = [&](uint64_t* bar) {
+                if (kPair) umma_commit_pair(bar);
+                else umma_commit(bar);
+            };
             uint32_t st = 0, ph = 0, it = 0, j = 0;
-            for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++j) {
+            for (int64_t tile = unit; tile < ntiles; tile += nunits, ++j) {
                 const uint32_t buf = nabuf == 2 ? (j & 1u) : 0u;
                 const uint32_t use = nabuf == 2 ? (j >> 1) : j;
                 mbar_wait(&ctl->a_full[buf], use & 1u, 3);
@@ -329,23 +370,22 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                         const int ksteps = rem >= BK ? BK / UK : (rem + UK - 1) / UK;
                         for (int k = 0; k < ksteps; ++k) {
                             const uint64_t da = make_sdesc_sw128(a_base + kb * A_KB_BYTES + k * (UK * 2));
-                            const uint64_t db = make_sdesc_sw128(b_addr + st * B_ST_BYTES + k * (UK * 2));
-                            umma_bf16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                            const uint64_t db = make_sdesc_sw128(b_addr + st * B_ST + k * (UK * 2));
+                            mma(d_tmem, da, db, (kb | k) != 0 ? 1u : 0u);
                         }
-                        umma_commit(&ctl->b_empty[st]);        // stage reusable once these MMAs retire
+                        commit(&ctl->b_empty[st]);             // stage reusable once these MMAs retire
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                     }
                     if (kMode == 3) {       // + [1,1,1,0..] x [h1,h2,h3,0..]^T = -||e||^2/2 into the same accumulator
                         mbar_wait(&ctl->b_full[st], ph, 5);
                         tc_fence_after();
-                        umma_bf16_ss(d_tmem, make_sdesc_none(smem_u32(smO), 128, 256),
-                                     make_sdesc_none(b_addr + st * B_ST_BYTES, 128, 256), idesc, 1u);
-                        umma_commit(&ctl->b_empty[st]);
+                        mma(d_tmem, make_sdesc_none(smem_u32(smO), 128, 256), make_sdesc_none(b_addr + st * B_ST, 128, 256), 1u);
+                        commit(&ctl->b_empty[st]);
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                     }
-                    umma_commit(&ctl->t_full[acc]);            // accumulator tile complete
+                    commit(&ctl->t_full[acc]);                 // accumulator tile complete
                 }
-                umma_commit(&ctl->a_empty[buf]);               // slab of z no longer read
+                commit(&ctl->a_empty[buf]);                    // slab of z no longer read
             }
         }
     } else if (warp >= 4) {
@@ -358,8 +398,17 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         const uint32_t nsm = smem_u32(smN);
         const uint32_t slot = smem_u32(smP) + (threadIdx.x - 128) * 16u;     // [2][epilogue threads] x 16 B: conflict-free
         constexpr uint32_t slot_stride = kEpiWarps * 32 * 16;
+        const uint32_t lead_t_empty = kPair ? map_to_cta(smem_u32(&ctl->t_empty[0]), 0) : 0u;       // [acc]: + 8 * acc
+        auto release_acc = [&](uint32_t acc) {      // this warp has read everything it needs from accumulator `acc`
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (kPair) mbar_arrive_cluster(lead_t_empty + 8u * acc);
+                else mbar_arrive(&ctl->t_empty[acc]);
+            }
+        };
         uint32_t it = 0, xb = 0;
-        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, xb ^= 1) {
+        for (int64_t tile = unit; tile < ntiles; tile += nunits, xb ^= 1) {
             float best = kMode == 3 ? -CUDART_INF_F : CUDART_INF_F;      // kMode 3 tracks a maximum
             int bi = 0;
             for (int nb = 0; nb < num_nb; ++nb, ++it) {
@@ -369,10 +418,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                 uint32_t ra[32], rb[32];
                 mbar_wait(&ctl->t_full[acc], acc_ph, 6);
                 tc_fence_after();
-                if (dbg == 2) {                       // timing experiment: no TMEM read, no fold
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&ctl->t_empty[acc]);
+                if (dbg == 2 || dbg == 4) {           // timing experiment: no TMEM read, no fold
+                    if (dbg == 2 || rank == 0) release_acc(acc);
                     continue;
                 }
                 tmem_ld_32x32b_x32(taddr, ra);
@@ -388,9 +435,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     tmem_wait_ld();
                 }
                 // every TMEM read of this accumulator has landed: hand it back before folding what is in registers
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&ctl->t_empty[acc]);
+                release_acc(acc);
                 if (dbg == 1) {                       // timing experiment: TMEM read but no fold
                     bi += (int)(ra[0] ^ rb[5] ^ ra[31] ^ rb[17]);
                     continue;
@@ -418,7 +463,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     const int oi = ctl->xidx[xb][p][rl];
                     if (ob < best) { best = ob; bi = oi; }
                 }
-                const int64_t row = tile * BM + rl;
+                const int64_t row = tile * SLAB + rank * BM + rl;
                 if (row < N) {
                     idx[row] = bi;
                     if (smin != nullptr) smin[row] = best;
@@ -429,7 +474,11 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+    if (kPair) cluster_sync_all();         // neither CTA leaves (or frees TMEM) while the other can still signal it
+    if (warp == 2) {
+        if (kPair) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+        else tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
 }
 
 // ---------------------------------------------------------------------------------- host
@@ -472,6 +521,28 @@ int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int D, int64_t ld,
     return VQ_OK;
 }
 
+// The aug image behind the norms, viewed as [K_pad / 64 rows][256 x u64] (2 KiB rows, no swizzle): a box of 2 rows is the
+// 4 KiB block of 128 consecutive codes (pair mode loads it through TMA so that completion can go to the leader's barrier).
+int make_tmap_aug(CUtensorMap* m, const void* base, int K_pad) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (enc == nullptr) {
+        set_error("cuTensorMapEncodeTiled entry point not available");
+        return VQ_ERR_CUDA;
+    }
+    cuuint64_t gdim[2] = {256, (cuuint64_t)(K_pad / 64)};
+    cuuint64_t gstr[1] = {2048};
+    cuuint32_t box[2] = {256, 2};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(aug) failed (CUresult %d) K_pad=%d", (int)r, K_pad);
+        return VQ_ERR_CUDA;
+    }
+    return VQ_OK;
+}
+
 }  // namespace
 
 bool assign_tc_supported(int64_t N, int D, int64_t ldz, int K) {
@@ -486,7 +557,7 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
                "vq_assign(bf16): z and E_bf16 must be 16-byte aligned");
     const int nkb = (D + BK - 1) / BK;
     const int num_nb = (K + BN - 1) / BN;
-    static int epi_warps = 0, dbg = 0, mode_override = -1;
+    static int epi_warps = 0, dbg = 0, mode_override = -1, pair_override = -1;
     if (epi_warps == 0) {
         const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // tuning knob: 8 or 16 epilogue warps
         epi_warps = (ev != nullptr && atoi(ev) == 8) ? 8 : 16;
@@ -494,7 +565,14 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
         if (ev != nullptr) dbg = atoi(ev);
         ev = getenv("VQ_ASSIGN_MODE");                           // force an epilogue mode (0..3)
         if (ev != nullptr) mode_override = atoi(ev);
+        ev = getenv("VQ_ASSIGN_PAIR");                           // 0: single-CTA kernel, 1: CTA-pair kernel
+        if (ev != nullptr) pair_override = atoi(ev);
     }
+    // CTA pairs (cta_group::2) whenever there is more than one 128-row slab: a pair retires 256 rows in the time one CTA
+    // retires 128, so the load balance over the SMs is the same and each SM pulls half the codebook bytes.
+    bool pair = N > BM;
+    if (pair_override == 0) pair = false;
+    if (pair_override == 1) pair = true;
     // Epilogue mode (see fold_chunk / fold_chunk_aug).  The epilogue, not the tensor pipe, bounds this kernel when
     // D is small (a 128 x 256 tile costs D/16 MMAs but always 32768 compare-selects), so:
     //   D <= 128          mode 3: ||e||^2 rides through the tensor core as one more K step, arg-max of the raw accumulator,
@@ -511,40 +589,87 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     const int park_bytes = 2 * epi_warps * 32 * 16;
     const int a_bytes = nkb * A_KB_BYTES;
     const int norm_bytes = num_nb * BN * 4;
+    const int b_st = pair ? B_ST_BYTES / 2 : B_ST_BYTES;           // a pair CTA holds half of every codebook stage
+    const int max_stages = pair ? MAX_STAGES : 6;
     int avail = 0, nabuf = 1, nstages = 0, extra = 0;
     bool norm_smem = false;
     for (;;) {
         extra = (mode >= 2 ? park_bytes : 0) + (mode == 3 ? 4096 : 0);
         avail = SMEM_LIMIT - 1024 - (int)sizeof(Ctl) - extra;
-        norm_smem = mode != 3 && K <= NORM_SMEM_MAX && (avail - a_bytes - norm_bytes) / B_ST_BYTES >= 3;
+        norm_smem = mode != 3 && K <= NORM_SMEM_MAX && (avail - a_bytes - norm_bytes) / b_st >= 3;
         const int after_norm = avail - (norm_smem ? norm_bytes : 0);
-        nabuf = (after_norm - 2 * a_bytes) / B_ST_BYTES >= 4 ? 2 : 1;
-        nstages = (after_norm - nabuf * a_bytes) / B_ST_BYTES;
-        if (nstages > 6) nstages = 6;
+        nabuf = (after_norm - 2 * a_bytes) / b_st >= 4 ? 2 : 1;
+        nstages = (after_norm - nabuf * a_bytes) / b_st;
+        if (nstages > max_stages) nstages = max_stages;
         if (nstages >= 3 || mode == 0) break;
         mode = mode == 3 ? 2 : 0;                      // not enough room for the ring: fall back to a leaner mode
     }
     VQ_REQUIRE(nstages >= 2, "vq_assign(bf16): D=%d leaves no room for the codebook ring", D);
-    const size_t smem_total = 1024 + (size_t)nabuf * a_bytes + (size_t)nstages * B_ST_BYTES +
+    const size_t smem_total = 1024 + (size_t)nabuf * a_bytes + (size_t)nstages * b_st +
                               (norm_smem ? norm_bytes : 0) + extra + sizeof(Ctl);
 
-    CUtensorMap tm_z, tm_e;
+    CUtensorMap tm_z, tm_e, tm_aug;
     int rc = make_tmap(&tm_z, z_bf16, N, D, ldz, BM);
     if (rc != VQ_OK) return rc;
-    rc = make_tmap(&tm_e, E_bf16, K, D, D, BN);
+    rc = make_tmap(&tm_e, E_bf16, K, D, D, pair ? BN / 2 : BN);
     if (rc != VQ_OK) return rc;
+    if (pair && mode == 3) {
+        rc = make_tmap_aug(&tm_aug, e_norm2 + num_nb * BN, num_nb * BN);
+        if (rc != VQ_OK) return rc;
+    } else {
+        tm_aug = tm_e;                                 // never dereferenced
+    }
 
-    const int64_t ntiles = (N + BM - 1) / BM;
-    const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
-    void (*kern)(const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int, int32_t*, float*, int);
-#define VQ_PICK(NS, EW)                                                                    \
-    (mode == 3 ? assign_tc_kernel<false, EW, 3> : mode == 2 ? assign_tc_kernel<NS, EW, 2> \
-                                              : mode == 1 ? assign_tc_kernel<NS, EW, 1> : assign_tc_kernel<NS, EW, 0>)
+    void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
+                 int32_t*, float*, int);
+#define VQ_PICK3(NS, EW, P)                                                                       \
+    (mode == 3 ? assign_tc_kernel<false, EW, 3, P> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P>  \
+                                                 : mode == 1 ? assign_tc_kernel<NS, EW, 1, P> : assign_tc_kernel<NS, EW, 0, P>)
+#define VQ_PICK(NS, EW) (pair ? VQ_PICK3(NS, EW, true) : VQ_PICK3(NS, EW, false))
     if (norm_smem) kern = epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
     else kern = epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
 #undef VQ_PICK
+#undef VQ_PICK3
     VQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    kern<<<grid, 128 + 32 * epi_warps, smem_total, st>>>(tm_z, tm_e, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg);
+
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    cfg.blockDim = dim3(128 + 32 * epi_warps);
+    cfg.dynamicSmemBytes = smem_total;
+    cfg.stream = st;
+    if (pair) {
+        const int64_t nslabs = (N + 2 * BM - 1) / (2 * BM);
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        // persistent: one pair per TPC that can host one (a TPC with a fused-off SM cannot)
+        static int max_pairs = 0;
+        static const void* cached_kern = nullptr;
+        static size_t cached_smem = 0;
+        if (max_pairs == 0 || cached_kern != (const void*)kern || cached_smem != smem_total) {
+            cached_kern = (const void*)kern;
+            cached_smem = smem_total;
+            cfg.gridDim = dim3((unsigned)(sm_count() & ~1));
+            int nc = 0;
+            if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) != cudaSuccess || nc <= 0) {
+                (void)cudaGetLastError();
+                nc = sm_count() / 2;
+            }
+            max_pairs = nc < sm_count() / 2 ? nc : sm_count() / 2;
+        }
+        cfg.gridDim = dim3((unsigned)(2 * (nslabs < max_pairs ? nslabs : max_pairs)));
+    } else {
+        const int64_t ntiles = (N + BM - 1) / BM;
+        cfg.gridDim = dim3((unsigned)(ntiles < sm_count() ? ntiles : sm_count()));
+    }
+    static const bool verbose = getenv("VQ_ASSIGN_VERBOSE") != nullptr;
+    if (verbose)
+        fprintf(stderr, "vq_assign: N=%lld K=%d D=%d pair=%d mode=%d nstages=%d nabuf=%d norm_smem=%d grid=%u smem=%zu\n",
+                (long long)N, K, D, (int)pair, mode, nstages, nabuf, (int)norm_smem, cfg.gridDim.x, smem_total);
+    VQ_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg));
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;
