@@ -47,7 +47,9 @@ enum {
 /* what vq_gather_st_loss_scatter accumulates per code */
 enum {
     VQ_STAT_SUM_Z = 0,  /* sum_k = sum z_n         (EMA statistics, a-5)                                 */
-    VQ_STAT_SUM_RESID = 1 /* sum_k = sum (z_n - e_k) (st mode: codebook gradient = -2g/(ND) * sum_k)     */
+    VQ_STAT_SUM_RESID = 1, /* sum_k = sum (z_n - e_k) (st mode: codebook gradient = -2g/(ND) * sum_k)     */
+    VQ_STAT_ACCUMULATE = 16 /* flag, OR-ed in: add to code_cnt / code_sum / sq_err_sum instead of overwriting them
+                               (a batch processed in row chunks, e.g. while the next chunk is still in flight) */
 };
 
 int vq_abi_version(void);

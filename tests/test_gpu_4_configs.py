@@ -115,3 +115,57 @@ def test_full_size_properties_c5():
     ref_idx, _ = R.assign(zs, E0.cpu(), "bf16")
     rep = R.near_tie_report(zs, E0.cpu(), idx[sel].cpu(), ref_idx, precision="bf16")
     assert rep["hard"] == 0, rep
+
+
+@pytest.mark.parametrize("D,dtype,det", [(64, torch.bfloat16, False), (64, torch.float32, True), (20, torch.float32, False),
+                                         (7, torch.float32, False)])
+def test_pass_accumulate_flag_equals_one_shot(D, dtype, det):
+    """VQ_STAT_ACCUMULATE: the pass over two row chunks adds up to the pass over the whole batch (vector path,
+    deterministic path and the generic odd-D path)."""
+    from vqvae_b200 import ops
+    from vqvae_b200._lib import VQ_STAT_SUM_Z
+    torch.manual_seed(D)
+    N, K = 5000, 96
+    E = torch.randn(K, D, device="cuda")
+    z = torch.randn(N, D, device="cuda").to(dtype)
+    idx = torch.randint(0, K, (N,), device="cuda", dtype=torch.int32)
+    ws = torch.empty(ops.workspace_bytes(N, K, D, dtype), dtype=torch.uint8, device="cuda")
+
+    def run(parts):
+        q = torch.empty_like(z); sq = torch.full((1,), 123.0, device="cuda")
+        cnt = torch.full((K,), 7.0, device="cuda"); sums = torch.full((K, D), 7.0, device="cuda")
+        for c, (a, b) in enumerate(parts):
+            ops.gather_st_loss_scatter(z[a:b], idx[a:b], E, q[a:b], sq, cnt, sums, VQ_STAT_SUM_Z, det, ws, accumulate=c > 0)
+        return q, sq, cnt, sums
+
+    q1, s1, c1, m1 = run([(0, N)])
+    q2, s2, c2, m2 = run([(0, 2048), (2048, 2048), (2048, N)])           # includes an empty chunk
+    assert torch.equal(q1, q2) and torch.equal(c1, c2)
+    np.testing.assert_allclose(float(s2), float(s1), rtol=1e-5)
+    np.testing.assert_allclose(m2.cpu().numpy(), m1.cpu().numpy(), rtol=1e-4, atol=1e-4)
+    ref_cnt, ref_sum = R.code_stats(z.float().cpu(), idx.long().cpu(), K)
+    assert torch.equal(c1.cpu(), ref_cnt)
+    np.testing.assert_allclose(m1.cpu().numpy(), ref_sum.numpy(), rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize("quantizer", ["ema", "st"])
+def test_forward_host_equals_forward_on_the_copied_batch(quantizer):
+    """The pipelined host entry (row chunks cross PCIe while the previous chunk is quantised) is the same step."""
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(8)
+    K, D, N = 512, 64, 300000
+    a = VectorQuantizer(D, K, quantizer=quantizer, deterministic=True).cuda()
+    b = VectorQuantizer(D, K, quantizer=quantizer, deterministic=True).cuda()
+    b.load_state_dict(a.state_dict())
+    for step in range(2):
+        zh = torch.randn(50, N // 50, D).to(torch.bfloat16).pin_memory()
+        with torch.no_grad():
+            qa, la, ia = a(zh.cuda())
+        qb, lb, ib = b.forward_host(zh, chunks=None if step == 0 else 3)
+        torch.cuda.synchronize()
+        assert qb.shape == zh.shape and ib.shape == zh.shape[:-1] and qb.is_cuda
+        assert torch.equal(ia, ib) and torch.equal(qa, qb)
+        np.testing.assert_allclose(float(lb), float(la), rtol=1e-5)
+        np.testing.assert_allclose(b.codebook.detach().cpu().numpy(), a.codebook.detach().cpu().numpy(), rtol=2e-5, atol=1e-6)
+        assert torch.equal(a.usage_total, b.usage_total)
+        np.testing.assert_allclose(float(b.perplexity), float(a.perplexity), rtol=1e-5)

@@ -1,9 +1,7 @@
 #!/bin/bash
-# scratch trip: pair (plain remote arrive) vs single on the named workloads, then the parity tests with pair on
-mkdir -p gpurun_out; rm -f gpurun_out/kern.log
-run() { echo "== $*" | tee -a gpurun_out/kern.log; env "$@" timeout 300 python tools/bench_kernels.py c2 c4 c1 c3 c5 2>&1 | grep -v "^vq_assign" | tail -n 5 | cut -c1-75 | tee -a gpurun_out/kern.log; }
-run VQ_ASSIGN_PAIR=1
-run VQ_ASSIGN_PAIR=0
-run VQ_ASSIGN_PAIR=1 VQ_ASSIGN_DBG=2
+mkdir -p gpurun_out
 timeout 900 python -m pytest tests -q -m gpu -x --timeout=300 > gpurun_out/tests.log 2>&1; echo "tests exit $?" >> gpurun_out/tests.log
-tail -n 4 gpurun_out/tests.log
+tail -n 12 gpurun_out/tests.log
+timeout 600 python bench.py --skip-cpu > gpurun_out/bench_c2.log 2>&1; echo "bench exit $?" >> gpurun_out/bench_c2.log
+timeout 600 python bench.py --workload c4 --skip-cpu > gpurun_out/bench_c4.log 2>&1; echo "bench exit $?" >> gpurun_out/bench_c4.log
+for f in bench_c2 bench_c4; do echo "== $f"; tail -n 3 gpurun_out/$f.log | cut -c1-1900; done

@@ -16,6 +16,7 @@ VQ_OK, VQ_ERR_ARG, VQ_ERR_CUDA, VQ_ERR_UNSUPPORTED = 0, 1, 2, 3
 VQ_DT_BF16, VQ_DT_F32 = 0, 1
 VQ_SEARCH_BF16, VQ_SEARCH_F32 = 0, 1
 VQ_STAT_SUM_Z, VQ_STAT_SUM_RESID = 0, 1
+VQ_STAT_ACCUMULATE = 16
 ABI_VERSION = 1
 MAX_PEERS, IPC_HANDLE_BYTES = 16, 64
 

@@ -112,7 +112,8 @@ int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int
                               vq_stream_t stream) {
     VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_gather_st_loss_scatter: bad in_dtype %d", in_dtype);
     VQ_REQUIRE(out_dtype == in_dtype, "vq_gather_st_loss_scatter: out_dtype must equal in_dtype");
-    VQ_REQUIRE(stat_kind == VQ_STAT_SUM_Z || stat_kind == VQ_STAT_SUM_RESID, "bad stat_kind %d", stat_kind);
+    VQ_REQUIRE((stat_kind & ~VQ_STAT_ACCUMULATE) == VQ_STAT_SUM_Z || (stat_kind & ~VQ_STAT_ACCUMULATE) == VQ_STAT_SUM_RESID,
+               "bad stat_kind %d", stat_kind);
     VQ_REQUIRE(E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (idx != nullptr && z != nullptr && q_out != nullptr)),
                "vq_gather_st_loss_scatter: NULL argument");
     return launch_gather_pass(z, in_dtype, N, D, ldz, idx, E_f32, K, q_out, ldq, sq_err_sum, code_cnt, code_sum,

@@ -425,13 +425,14 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                 tmem_ld_32x32b_x32(taddr, ra);
                 tmem_ld_32x32b_x32(taddr + 32, rb);
                 tmem_wait_ld();
-                if (CW == 128) {
-                    if (kMode == 3) fold_chunk_aug(ra, col0, best, bi, slot, slot_stride);
-                    else fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0, best, bi, slot, slot_stride, dbg);
-                    tmem_ld_32x32b_x32(taddr + 64, ra);          // in flight while the second chunk is folded
-                    if (kMode == 3) fold_chunk_aug(rb, col0 + 32, best, bi, slot, slot_stride);
-                    else fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + 32, best, bi, slot, slot_stride, dbg);
-                    tmem_ld_32x32b_x32(taddr + 96, rb);
+#pragma unroll
+                for (int c = 0; c + 2 < CW / 32; c += 2) {        // CW = 128 / 256: more chunk pairs before the last one
+                    if (kMode == 3) fold_chunk_aug(ra, col0 + 32 * c, best, bi, slot, slot_stride);
+                    else fold_chunk<kNormSmem, kMode>(ra, norms, nsm, col0 + 32 * c, best, bi, slot, slot_stride, dbg);
+                    tmem_ld_32x32b_x32(taddr + 32 * (c + 2), ra);    // in flight while the second chunk is folded
+                    if (kMode == 3) fold_chunk_aug(rb, col0 + 32 * (c + 1), best, bi, slot, slot_stride);
+                    else fold_chunk<kNormSmem, kMode>(rb, norms, nsm, col0 + 32 * (c + 1), best, bi, slot, slot_stride, dbg);
+                    tmem_ld_32x32b_x32(taddr + 32 * (c + 3), rb);
                     tmem_wait_ld();
                 }
                 // every TMEM read of this accumulator has landed: hand it back before folding what is in registers
@@ -557,10 +558,10 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
                "vq_assign(bf16): z and E_bf16 must be 16-byte aligned");
     const int nkb = (D + BK - 1) / BK;
     const int num_nb = (K + BN - 1) / BN;
-    static int epi_warps = 0, dbg = 0, mode_override = -1, pair_override = -1;
-    if (epi_warps == 0) {
-        const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // tuning knob: 8 or 16 epilogue warps
-        epi_warps = (ev != nullptr && atoi(ev) == 8) ? 8 : 16;
+    static int env_epi = -1, dbg = 0, mode_override = -1, pair_override = -1;
+    if (env_epi < 0) {
+        const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // tuning knob: 4, 8 or 16 epilogue warps
+        env_epi = (ev != nullptr && (atoi(ev) == 16 || atoi(ev) == 8 || atoi(ev) == 4)) ? atoi(ev) : 0;
         ev = getenv("VQ_ASSIGN_DBG");                            // 1/2/3: timing experiments, results are WRONG
         if (ev != nullptr) dbg = atoi(ev);
         ev = getenv("VQ_ASSIGN_MODE");                           // force an epilogue mode (0..3)
@@ -573,6 +574,8 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     bool pair = N > BM;
     if (pair_override == 0) pair = false;
     if (pair_override == 1) pair = true;
+    // epilogue warps (measured on B200): pairs 8 (C4 1409 us / C2 277 us; 16: 1427 / 292; 4: 1471 / 323), single CTA 16
+    const int epi_warps = env_epi != 0 ? env_epi : (pair ? 8 : 16);
     // Epilogue mode (see fold_chunk / fold_chunk_aug).  The epilogue, not the tensor pipe, bounds this kernel when
     // D is small (a 128 x 256 tile costs D/16 MMAs but always 32768 compare-selects), so:
     //   D <= 128          mode 3: ||e||^2 rides through the tensor core as one more K step, arg-max of the raw accumulator,
@@ -626,8 +629,8 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     (mode == 3 ? assign_tc_kernel<false, EW, 3, P> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P>  \
                                                  : mode == 1 ? assign_tc_kernel<NS, EW, 1, P> : assign_tc_kernel<NS, EW, 0, P>)
 #define VQ_PICK(NS, EW) (pair ? VQ_PICK3(NS, EW, true) : VQ_PICK3(NS, EW, false))
-    if (norm_smem) kern = epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
-    else kern = epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
+    if (norm_smem) kern = epi_warps == 4 ? VQ_PICK(true, 4) : epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
+    else kern = epi_warps == 4 ? VQ_PICK(false, 4) : epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
 #undef VQ_PICK
 #undef VQ_PICK3
     VQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));

@@ -465,7 +465,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
                             for (int x = 0; x < EPV; ++x) {
                                 const float d = zf[x] - e[j][x];
                                 loss = fmaf(d, d, loss);
-                                acc[j][x] += stat_kind == VQ_STAT_SUM_RESID ? d : zf[x];
+                                acc[j][x] += (stat_kind & 15) == VQ_STAT_SUM_RESID ? d : zf[x];
                             }
                             st_stream_16(q + (int64_t)r * ldq + v * EPV, qv[j]);
                         }
@@ -513,7 +513,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
             double tot = 0.0;
 #pragma unroll
             for (int i = 0; i < 8; ++i) tot += red[i];
-            sq_err_out[0] = (float)tot;
+            sq_err_out[0] = (stat_kind & VQ_STAT_ACCUMULATE) ? sq_err_out[0] + (float)tot : (float)tot;
             *done = 0;
         }
     }
@@ -549,7 +549,7 @@ pass_generic_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int3
                 const float zf = (float)z[row * ldz + d];
                 const float df = zf - ev;
                 loss = fmaf(df, df, loss);
-                if (code_sum != nullptr) atomicAdd(code_sum + (int64_t)c * D + d, stat_kind == VQ_STAT_SUM_RESID ? df : zf);
+                if (code_sum != nullptr) atomicAdd(code_sum + (int64_t)c * D + d, (stat_kind & 15) == VQ_STAT_SUM_RESID ? df : zf);
             }
         }
         if (!bad && lane == 0 && code_cnt != nullptr) atomicAdd(code_cnt + c, 1.f);
@@ -561,7 +561,7 @@ pass_generic_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int3
 // deterministic mode: code_sum[k] = sum over the slices that hold rows of code k, in slice order (one warp per code)
 __global__ void __launch_bounds__(256)
 reduce_dpart_kernel(const float* __restrict__ dpart, const int* __restrict__ start, int K, int D,
-                    float* __restrict__ code_sum) {
+                    float* __restrict__ code_sum, int accumulate) {
     const int lane = threadIdx.x & 31;
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (k >= K) return;
@@ -570,13 +570,13 @@ reduce_dpart_kernel(const float* __restrict__ dpart, const int* __restrict__ sta
         float acc = 0.f;
         if (b > a)
             for (int sl = a / LG; sl <= (b - 1) / LG; ++sl) acc += dpart[((int64_t)sl + k) * D + d];
-        code_sum[(int64_t)k * D + d] = acc;
+        code_sum[(int64_t)k * D + d] = accumulate ? code_sum[(int64_t)k * D + d] + acc : acc;
     }
 }
 
 // fixed-order reduction of the per-warp partial sums (double accumulate) -> out[0]
 __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ part, int64_t n,
-                                                               float* __restrict__ out) {
+                                                               float* __restrict__ out, int accumulate) {
     __shared__ double sh[32];
     double s = 0.0;
     for (int64_t i = threadIdx.x; i < n; i += 1024) s += (double)part[i];
@@ -588,7 +588,7 @@ __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __re
         s = sh[threadIdx.x];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (threadIdx.x == 0) out[0] = (float)s;
+        if (threadIdx.x == 0) out[0] = accumulate ? out[0] + (float)s : (float)s;
     }
 }
 
@@ -661,7 +661,9 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                "vq_gather_st_loss_scatter: bad shape N=%lld D=%d K=%d", (long long)N, D, K);
     VQ_REQUIRE((code_cnt == nullptr) == (code_sum == nullptr), "code_cnt and code_sum must both be given or both NULL");
     const bool stats = code_cnt != nullptr;
+    const bool accum = (stat_kind & VQ_STAT_ACCUMULATE) != 0;    // add to code_cnt / code_sum / sq_err_sum instead of overwriting
     if (N == 0) {
+        if (accum) return VQ_OK;
         if (stats) {
             VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
             VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
@@ -692,7 +694,7 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     if (!vec_ok) {
         const int64_t blocks = ceil_div64(N, 8);
         nparts = N;
-        if (stats) {
+        if (stats && !accum) {
             VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
             VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
         }
@@ -736,7 +738,8 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                 hist_smem_kernel<<<nb, 512, (size_t)K * 4, st>>>(idx, N, K, R, cnt_i);
                 scan_scatter_smem_kernel<<<nb, 512, (size_t)K * 12, st>>>(idx, N, K, R, cnt_i, cursor, perm,
                                                                           reinterpret_cast<float4*>(code_sum),
-                                                                          (int64_t)K * D / 4, code_cnt, K);
+                                                                          accum ? 0 : (int64_t)K * D / 4, code_cnt,
+                                                                          accum ? 0 : K);
                 count_launch(2);
                 stats_cleared = true;
             } else {
@@ -748,7 +751,7 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
             }
             VQ_CHECK_CUDA(cudaGetLastError());
             perm_arg = perm;
-            if (!stats_cleared) {
+            if (!stats_cleared && !accum) {
                 VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
                 VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
             }
@@ -763,13 +766,13 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
         if (dpart != nullptr) {
-            reduce_dpart_kernel<<<(K + 7) / 8, 256, 0, st>>>(dpart, start, K, D, code_sum);
+            reduce_dpart_kernel<<<(K + 7) / 8, 256, 0, st>>>(dpart, start, K, D, code_sum, accum ? 1 : 0);
             VQ_CHECK_CUDA(cudaGetLastError());
             count_launch();
         }
         return VQ_OK;                       // sq_err_sum was written by the pass kernel's last block
     }
-    reduce_partials_kernel<<<1, 1024, 0, st>>>(part, nparts, sq_err_sum);
+    reduce_partials_kernel<<<1, 1024, 0, st>>>(part, nparts, sq_err_sum, accum ? 1 : 0);
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

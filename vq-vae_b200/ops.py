@@ -87,8 +87,11 @@ def assign(z: torch.Tensor, E: torch.Tensor, E_bf16: Optional[torch.Tensor], e_n
 def gather_st_loss_scatter(z: torch.Tensor, idx: torch.Tensor, E: torch.Tensor, q_out: torch.Tensor,
                            sq_err_sum: torch.Tensor, code_cnt: Optional[torch.Tensor],
                            code_sum: Optional[torch.Tensor], stat_kind: int, deterministic: bool,
-                           ws: Optional[torch.Tensor]) -> None:
+                           ws: Optional[torch.Tensor], accumulate: bool = False) -> None:
+    """accumulate: add to sq_err_sum / code_cnt / code_sum instead of overwriting (row chunks of one batch)."""
     _need_cuda(z, idx, E, q_out, sq_err_sum, code_cnt, code_sum, ws)
+    if accumulate:
+        stat_kind |= _lib.VQ_STAT_ACCUMULATE
     N, D, ld = _rows(z)
     _, _, ldq = _rows(q_out)
     K = E.shape[0]

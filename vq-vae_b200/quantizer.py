@@ -340,6 +340,74 @@ class VectorQuantizer(nn.Module):
                 q = q.to(in_dtype)
             return q.reshape(*lead, self.emb_dim), loss, idx.reshape(lead)
 
+    @torch.no_grad()
+    def forward_host(self, z_host: torch.Tensor, chunks: Optional[int] = None):
+        """Quantise a batch that lives in (pinned) HOST memory: `[..., D]` CPU tensor in, device tensors
+        `(quantized, loss, indices)` out.  The batch is cut into row chunks; chunk c + 1 crosses PCIe on a copy stream
+        while the kernels work on chunk c (the search per chunk, the gather / loss / statistics pass accumulating
+        across chunks with VQ_STAT_ACCUMULATE), then one EMA update for the whole batch -- the same arithmetic as
+        `forward` on the copied tensor, with the transfer hidden behind the compute instead of in front of it.
+        Inference / EMA training only (no autograd graph: the input is not a device tensor)."""
+        if z_host.is_cuda:
+            raise ValueError("forward_host takes a CPU tensor; call forward() for device tensors")
+        if self.channel_first:
+            raise ValueError("forward_host expects channel-last rows [..., D]")
+        if z_host.shape[-1] != self.emb_dim:
+            raise ValueError(f"last dimension {z_host.shape[-1]} != emb_dim {self.emb_dim}")
+        if z_host.dtype not in (torch.bfloat16, torch.float32):
+            z_host = z_host.to(torch.float32)
+        dev = self.codebook.device
+        if dev.type != "cuda":
+            raise RuntimeError("VectorQuantizer.forward_host: the module must live on a CUDA device (no CPU fallback)")
+        lead, D, K = z_host.shape[:-1], self.emb_dim, self.codebook_size
+        zh = z_host.reshape(-1, D)
+        if not zh.is_contiguous():
+            zh = zh.contiguous()
+        if not zh.is_pinned():
+            zh = zh.pin_memory()
+        N = zh.shape[0]
+        if chunks is None:                      # ~128 K rows per chunk: transfer time per chunk well above launch costs
+            chunks = max(1, min(16, N // 131072))
+        rows = max(128, -(-N // max(1, chunks)) // 128 * 128) if N > 0 else 1
+        bounds = [(s, min(N, s + rows)) for s in range(0, max(N, 1), rows)] if N > 0 else []
+        search = self._search_for(zh.dtype)
+        self._ensure_shadow(search)
+        cur = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_stream", None) is None or self._copy_stream.device != dev:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        copy = self._copy_stream
+        z_dev = torch.empty((N, D), dtype=zh.dtype, device=dev)
+        q = torch.empty((N, D), dtype=zh.dtype, device=dev)
+        idx32 = torch.empty(N, dtype=torch.int32, device=dev)
+        sqerr = torch.zeros(1, dtype=torch.float32, device=dev)
+        stats = self._stats_buffer()
+        code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
+        ws = self._workspace(rows if N > 0 else 0, zh.dtype)
+        E = self.codebook.detach()
+        kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
+        copy.wait_stream(cur)                   # the fresh device buffers are not reused memory still in flight
+        landed = []
+        with torch.cuda.stream(copy):
+            for a, b in bounds:
+                z_dev[a:b].copy_(zh[a:b], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy)
+                landed.append(ev)
+        for c, (a, b) in enumerate(bounds):
+            cur.wait_event(landed[c])
+            ops.assign(z_dev[a:b], E, self._E_bf16, self._e_norm2, search, idx32[a:b], None, ws)
+            ops.gather_st_loss_scatter(z_dev[a:b], idx32[a:b], E, q[a:b], sqerr, code_cnt, code_sum, kind,
+                                       self.deterministic, ws, accumulate=c > 0)
+        if not bounds:
+            ops.gather_st_loss_scatter(z_dev, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws)
+        z_dev.record_stream(copy)
+        w = (1.0 + self.beta) if self.quantizer == "st" else self.beta
+        loss = (sqerr * (w / float(max(N * D, 1)))).reshape(())
+        self._finish_step(code_cnt, code_sum, search, ws)
+        if q.dtype != z_host.dtype:
+            q = q.to(z_host.dtype)
+        return q.reshape(*lead, D), loss, idx32.to(torch.int64).reshape(lead)
+
     def _forward_channel_first(self, z: torch.Tensor):
         if z.dim() < 2 or z.shape[1] != self.emb_dim:
             raise ValueError(f"channel_first: dimension 1 is {tuple(z.shape)[1:2]}, expected emb_dim {self.emb_dim}")
