@@ -239,14 +239,14 @@ def run_native(args, wl):
         step_resident()
     barrier()
     clocks = ClockSampler(local); clocks.start()
-    l0 = ops.launch_count()
+    l0 = ops.launch_count() + mod.graph_launches        # eager launches + launches replayed inside CUDA graphs
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step_resident()
     e1.record()
     barrier()
-    launches = ops.launch_count() - l0
+    launches = ops.launch_count() + mod.graph_launches - l0
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)

@@ -169,3 +169,37 @@ def test_forward_host_equals_forward_on_the_copied_batch(quantizer):
         np.testing.assert_allclose(b.codebook.detach().cpu().numpy(), a.codebook.detach().cpu().numpy(), rtol=2e-5, atol=1e-6)
         assert torch.equal(a.usage_total, b.usage_total)
         np.testing.assert_allclose(float(b.perplexity), float(a.perplexity), rtol=1e-5)
+
+
+@pytest.mark.parametrize("quantizer,dtype", [("ema", torch.bfloat16), ("st", torch.float32), ("ema", torch.float32)])
+def test_cuda_graph_replay_equals_eager(quantizer, dtype):
+    """Small batches replay the whole step as one CUDA graph from the third call on; results are those of the eager
+    launches, training and eval, with a larger batch (workspace regrowth) in between."""
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(9)
+    K, D = 128, 32
+    a = VectorQuantizer(D, K, quantizer=quantizer, deterministic=True, cuda_graph=True).cuda()
+    b = VectorQuantizer(D, K, quantizer=quantizer, deterministic=True, cuda_graph=False).cuda()
+    b.load_state_dict(a.state_dict())
+    g = torch.Generator().manual_seed(3)
+    sizes = [4096, 4096, 4096, 4096, 50000, 4096, 4096, 777, 777, 777]
+    for step, n in enumerate(sizes):
+        if step == 7:
+            a.eval(); b.eval()
+        z = torch.randn(n, D, generator=g).to(dtype).cuda()
+        outs = []
+        for m in (a, b):
+            x = z.clone().requires_grad_(True)
+            q, loss, idx = m(x)
+            (q.float().pow(2).sum() + 3.0 * loss).backward()
+            outs.append((q.detach(), loss.detach(), idx, x.grad, None if m.codebook.grad is None else m.codebook.grad.clone()))
+            if m.codebook.grad is not None:
+                with torch.no_grad():
+                    m.codebook -= 0.05 * m.codebook.grad
+                m.codebook.grad = None
+        for u, v in zip(*outs):
+            assert (u is None and v is None) or torch.equal(u, v), step
+        assert torch.equal(a.codebook, b.codebook) and torch.equal(a.usage_total, b.usage_total)
+        assert torch.equal(a.last_perplexity, b.last_perplexity) and torch.equal(a.ema_sum, b.ema_sum)
+    assert any(not isinstance(v, str) for v in a._graphs.values())      # a graph was really captured and replayed
+    assert not b._graphs

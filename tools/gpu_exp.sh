@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for w in c3 c5 c1; do
-timeout 600 python bench.py --workload $w --skip-cpu $( [ $w = c5 ] && echo "--steps 10" ) > gpurun_out/bench_$w.log 2>&1; echo "exit $?" >> gpurun_out/bench_$w.log
-echo "== $w"; tail -n 2 gpurun_out/bench_$w.log | cut -c1-1500
-done
+timeout 900 python -m pytest tests -q -m gpu -x --timeout=300 > gpurun_out/tests.log 2>&1; echo "tests exit $?" >> gpurun_out/tests.log
+tail -n 15 gpurun_out/tests.log
+timeout 300 python bench.py --workload c1 --skip-cpu > gpurun_out/bench_c1.log 2>&1; tail -n 1 gpurun_out/bench_c1.log | cut -c1-400
+timeout 300 python bench.py --skip-cpu --steps 20 > gpurun_out/bench_c2.log 2>&1; tail -n 1 gpurun_out/bench_c2.log | cut -c1-300

@@ -30,6 +30,8 @@ from ._lib import VQ_STAT_SUM_RESID, VQ_STAT_SUM_Z
 
 DEFAULT_DEAD_AFTER = 100
 PEER_ONE_SHOT_MAX_BYTES = 16 << 20      # total bytes a rank reads from its peers per step on the fused path
+GRAPH_MAX_BYTES = 32 << 20              # batches up to this size replay the step as one CUDA graph (launch-latency bound)
+GRAPH_CACHE = 4                         # captured (shape, mode) combinations kept per module
 
 
 class CodebookManager:
@@ -78,23 +80,12 @@ class _VQFunction(torch.autograd.Function):
         K = mod.codebook_size
         search = mod._search_for(z2.dtype)
         mod._ensure_shadow(search)
-        ws = mod._workspace(N, z2.dtype)
-        idx32 = torch.empty(N, dtype=torch.int32, device=z2.device)
-        q = torch.empty((N, D), dtype=z2.dtype, device=z2.device)
-        stats = mod._stats_buffer()
-        code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
-        sqerr = torch.empty(1, dtype=torch.float32, device=z2.device)
-        E = codebook.detach()
-        ops.assign(z2, E, mod._E_bf16, mod._e_norm2, search, idx32, None, ws)
-        kind = VQ_STAT_SUM_RESID if mod.quantizer == "st" else VQ_STAT_SUM_Z
-        ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, mod.deterministic, ws)
+        q, sqerr, idx, code_sum = mod._run_step(z2, search)
         w = (1.0 + mod.beta) if mod.quantizer == "st" else mod.beta
         loss = (sqerr * (w / float(max(N * D, 1)))).reshape(())
         ctx.save_for_backward(z2, q)
         ctx.mod, ctx.N, ctx.D = mod, N, D
         ctx.resid = code_sum.clone() if (mod.quantizer == "st" and codebook.requires_grad) else None
-        mod._finish_step(code_cnt, code_sum, search, ws)          # a-6 .. a-9
-        idx = idx32.to(torch.int64)
         ctx.mark_non_differentiable(idx)
         return q, loss, idx
 
@@ -142,6 +133,9 @@ class VectorQuantizer(nn.Module):
     deterministic: code-sorted visiting order reproducible run to run (stable counting sort).
     channel_first: forward takes [B, D, *spatial] (the live model's layout, frl/models/representation.py:317-334)
         and returns quantized in the same layout, indices [B, *spatial]; one transpose pass each way (a-0).
+    cuda_graph: small batches (<= 32 MB of latents, single process) replay the whole step -- search, sort, pass, EMA update,
+        index widening -- as ONE captured CUDA graph from the second call with the same shape on: at the reference's own
+        batch sizes (8 patches = 40 960 vectors) the step is launch-latency bound, not kernel bound.
     peer_exchange: "auto" (default) uses the fused peer-memory exchange (parallel.PeerExchange + vq_ema_update_dp)
         for the EMA statistics when the process group runs NCCL on one node, "nccl" always all-reduces with
         torch.distributed, "peer" insists on the fused path.
@@ -152,7 +146,8 @@ class VectorQuantizer(nn.Module):
     def __init__(self, emb_dim: int, codebook_size: int, beta: float = 0.25, quantizer: str = "st",
                  ema_decay: float = 0.99, ema_eps: float = 1e-5, search: str = "auto",
                  dead_after: int = DEFAULT_DEAD_AFTER, deterministic: bool = False, process_group=None,
-                 sync_stats: bool = True, channel_first: bool = False, peer_exchange: str = "auto"):
+                 sync_stats: bool = True, channel_first: bool = False, peer_exchange: str = "auto",
+                 cuda_graph: bool = True):
         super().__init__()
         if quantizer not in ("st", "ema"):
             raise ValueError(f"quantizer must be 'st' or 'ema', got {quantizer!r}")
@@ -186,6 +181,9 @@ class VectorQuantizer(nn.Module):
         # scratch (never in the state dict)
         self._E_bf16 = self._e_norm2 = self._ws = self._stats = None
         self._shadow_key = None
+        self.cuda_graph = bool(cuda_graph)
+        self._graphs: dict = {}
+        self.graph_launches = 0          # library kernels launched through graph replays (ops.launch_count sees only eager ones)
 
     # ------------------------------------------------------------------ reference-script surface
     def attach_codebook_manager(self, manager) -> None:
@@ -294,6 +292,77 @@ class VectorQuantizer(nn.Module):
 
     def _dist_active(self) -> bool:
         return self.sync_stats and parallel.dist_active(self.process_group)
+
+    # ------------------------------------------------------------------ one step of kernels (eager or as a CUDA graph)
+    def _step_kernels(self, z2, q, idx32, idx64, sqerr, search: str):
+        """a-1 .. a-9 on preallocated tensors; every launch goes to the current stream (capturable)."""
+        N, D = z2.shape
+        K = self.codebook_size
+        ws = self._workspace(N, z2.dtype)
+        stats = self._stats_buffer()
+        code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
+        E = self.codebook.detach()
+        ops.assign(z2, E, self._E_bf16, self._e_norm2, search, idx32, None, ws)
+        kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
+        ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws)
+        self._finish_step(code_cnt, code_sum, search, ws)
+        idx64.copy_(idx32)
+        return code_sum
+
+    def _graph_wanted(self, z2) -> bool:
+        return (self.cuda_graph and z2.shape[0] > 0 and z2.numel() * z2.element_size() <= GRAPH_MAX_BYTES
+                and not parallel.dist_active(self.process_group) and self._peers is None
+                and not torch.cuda.is_current_stream_capturing())
+
+    def _run_step(self, z2, search: str):
+        """-> (q, sq_err_sum, idx int64, code_sum view).  Small single-process batches: first call with a given shape
+        runs eagerly (it is also the warm-up), the second captures the step into a CUDA graph, later ones replay it."""
+        N, D = z2.shape
+        dev = z2.device
+        if self._graph_wanted(z2):
+            # every address the captured launches hold is part of the key: a moved module, a regrown workspace or a
+            # re-created shadow simply never matches the stale entry again
+            key = (N, z2.dtype, search, self.training, self.quantizer, self.deterministic, self.codebook.data_ptr(),
+                   self.ema_sum.data_ptr(), self._E_bf16.data_ptr() if self._E_bf16 is not None else 0,
+                   self._e_norm2.data_ptr(), self._workspace(N, z2.dtype).data_ptr(), self._stats_buffer().data_ptr(),
+                   dev.index)
+            ent = self._graphs.get(key)
+            if ent is None:
+                if len(self._graphs) >= GRAPH_CACHE:
+                    self._graphs.clear()
+                self._graphs[key] = "seen"
+            else:
+                if ent == "seen":
+                    ent = self._capture_step(z2, search)
+                    self._graphs[key] = ent
+                g, sz, sq_, si32, si64, ssq, code_sum, n_launch = ent
+                sz.copy_(z2)
+                g.replay()
+                self.graph_launches += n_launch
+                return sq_.clone(), ssq.clone(), si64.clone(), code_sum
+        q = torch.empty((N, D), dtype=z2.dtype, device=dev)
+        idx32 = torch.empty(N, dtype=torch.int32, device=dev)
+        idx64 = torch.empty(N, dtype=torch.int64, device=dev)
+        sqerr = torch.empty(1, dtype=torch.float32, device=dev)
+        code_sum = self._step_kernels(z2, q, idx32, idx64, sqerr, search)
+        return q, sqerr, idx64, code_sum
+
+    def _capture_step(self, z2, search: str):
+        N, D = z2.shape
+        dev = z2.device
+        sz = torch.empty((N, D), dtype=z2.dtype, device=dev)
+        sq_ = torch.empty((N, D), dtype=z2.dtype, device=dev)
+        si32 = torch.empty(N, dtype=torch.int32, device=dev)
+        si64 = torch.empty(N, dtype=torch.int64, device=dev)
+        ssq = torch.empty(1, dtype=torch.float32, device=dev)
+        self._workspace(N, z2.dtype)                 # sized before capture: the graph holds its address
+        self._stats_buffer()
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize(dev)
+        l0 = ops.launch_count()
+        with torch.cuda.graph(g):                    # records, does not execute: module state is untouched
+            code_sum = self._step_kernels(sz, sq_, si32, si64, ssq, search)
+        return (g, sz, sq_, si32, si64, ssq, code_sum, ops.launch_count() - l0)
 
     # ------------------------------------------------------------------ a-6 .. a-9
     def _finish_step(self, code_cnt, code_sum, search: str, ws) -> None:
