@@ -571,9 +571,11 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     }
     // CTA pairs (cta_group::2) whenever there is more than one 128-row slab: a pair retires 256 rows in the time one CTA
     // retires 128, so the load balance over the SMs is the same and each SM pulls half the codebook bytes.
-    bool pair = N > BM;
+    static bool pair_unavailable = false;            // set once if this device / context cannot co-schedule CTA pairs
+    bool pair = N > BM && !pair_unavailable;
     if (pair_override == 0) pair = false;
     if (pair_override == 1) pair = true;
+  for (int attempt = 0; attempt < 2; ++attempt) {    // second round only if the pair launch turned out to be impossible
     // epilogue warps (measured on B200): pairs 8 (C4 1409 us / C2 277 us; 16: 1427 / 292; 4: 1471 / 323), single CTA 16
     const int epi_warps = env_epi != 0 ? env_epi : (pair ? 8 : 16);
     // Epilogue mode (see fold_chunk / fold_chunk_aug).  The epilogue, not the tensor pipe, bounds this kernel when
@@ -658,8 +660,11 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
             cfg.gridDim = dim3((unsigned)(sm_count() & ~1));
             int nc = 0;
             if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) != cudaSuccess || nc <= 0) {
-                (void)cudaGetLastError();
-                nc = sm_count() / 2;
+                (void)cudaGetLastError();            // no room for a single pair (MPS slice, odd partition, ...): single-CTA kernel
+                max_pairs = 0;
+                pair_unavailable = true;
+                pair = false;
+                continue;
             }
             max_pairs = nc < sm_count() / 2 ? nc : sm_count() / 2;
         }
@@ -672,10 +677,20 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     if (verbose)
         fprintf(stderr, "vq_assign: N=%lld K=%d D=%d pair=%d mode=%d nstages=%d nabuf=%d norm_smem=%d grid=%u smem=%zu\n",
                 (long long)N, K, D, (int)pair, mode, nstages, nabuf, (int)norm_smem, cfg.gridDim.x, smem_total);
-    VQ_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg));
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg);
+    if (le != cudaSuccess && pair && attempt == 0) {  // cluster launch refused: fall back to the single-CTA kernel for good
+        (void)cudaGetLastError();
+        pair_unavailable = true;
+        pair = false;
+        continue;
+    }
+    VQ_CHECK_CUDA(le);
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;
+  }
+    set_error("vq_assign(bf16): kernel launch failed");
+    return VQ_ERR_CUDA;
 }
 
 }  // namespace vq
