@@ -1,5 +1,6 @@
 #!/bin/bash
+# 8-GPU trip: bench at N=8 (c2, c4), kept short
 mkdir -p gpurun_out
-timeout 600 python tools/bench_eager_gpu.py c2 c4 c1 > gpurun_out/eager_gpu.log 2>&1; echo "exit $?" >> gpurun_out/eager_gpu.log; cat gpurun_out/eager_gpu.log
-timeout 600 python -m pytest tests/test_gpu_2_tensorcore.py tests/test_gpu_4_configs.py -q -x --timeout=300 2>&1 | tail -n 2
-timeout 300 python bench.py --skip-cpu --steps 20 2>&1 | tail -n 1 | cut -c1-250
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus 8 --steps 20 --warmup 5 > gpurun_out/bench8_c2.log 2>&1; echo "exit $?" >> gpurun_out/bench8_c2.log
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29542 bench.py --gpus 8 --steps 20 --warmup 5 --workload c4 > gpurun_out/bench8_c4.log 2>&1; echo "exit $?" >> gpurun_out/bench8_c4.log
+for f in bench8_c2 bench8_c4; do echo "== $f"; tail -n 2 gpurun_out/$f.log | cut -c1-900; done
