@@ -74,10 +74,24 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
     int dead = 0;
     if (kPeer) {
         peers_signal_and_wait(P);
-        for (int k = t; k < K; k += 1024) {
-            float c = 0.f;
-            for (int r = 0; r < P.world; ++r) c = __fadd_rn(c, ld_peer(P.stats[r] + KD + k));
-            cnt_red[k] = c;
+        // all ranks' values of a batch are requested before the first is used (one NVLink round trip per batch, not one
+        // per rank); the adds then run in rank order, so every rank forms bit-identical sums
+        constexpr int KB = 4;
+        for (int k0 = t; k0 < K; k0 += 1024 * KB) {
+            float v[KB][VQ_MAX_PEERS];
+#pragma unroll
+            for (int b = 0; b < KB; ++b)
+#pragma unroll
+                for (int r = 0; r < VQ_MAX_PEERS; ++r)
+                    v[b][r] = (r < P.world && k0 + 1024 * b < K) ? ld_peer(P.stats[r] + KD + k0 + 1024 * b) : 0.f;
+#pragma unroll
+            for (int b = 0; b < KB; ++b) {
+                float c = 0.f;
+#pragma unroll
+                for (int r = 0; r < VQ_MAX_PEERS; ++r)
+                    if (r < P.world) c = __fadd_rn(c, v[b][r]);
+                if (k0 + 1024 * b < K) cnt_red[k0 + 1024 * b] = c;
+            }
         }
         __syncthreads();
         code_cnt = cnt_red;
@@ -189,28 +203,44 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
         if (lane == 0) ema_cnt[k] = n;
     }
     float nrm = 0.f;
-    for (int d = lane; d < D; d += 32) {
-        const int64_t o = (int64_t)k * D + d;
-        float ev;
-        if (do_ema) {
-            float cs;
-            if (kPeer) {
-                cs = 0.f;
-                for (int r = 0; r < P.world; ++r) cs = __fadd_rn(cs, ld_peer(P.stats[r] + o));
-            } else {
-                cs = code_sum[o];
+    constexpr int DB = 4;                     // elements per lane whose peer loads are in flight together
+    for (int d0 = lane; d0 < D; d0 += 32 * DB) {
+        float cs[DB];
+        if (do_ema && kPeer) {                // one NVLink round trip for DB x world values, adds in rank order
+            float v[DB][VQ_MAX_PEERS];
+#pragma unroll
+            for (int b = 0; b < DB; ++b)
+#pragma unroll
+                for (int r = 0; r < VQ_MAX_PEERS; ++r)
+                    v[b][r] = (r < P.world && d0 + 32 * b < D) ? ld_peer(P.stats[r] + (int64_t)k * D + d0 + 32 * b) : 0.f;
+#pragma unroll
+            for (int b = 0; b < DB; ++b) {
+                cs[b] = 0.f;
+#pragma unroll
+                for (int r = 0; r < VQ_MAX_PEERS; ++r)
+                    if (r < P.world) cs[b] = __fadd_rn(cs[b], v[b][r]);
             }
-            const float m = __fadd_rn(__fmul_rn(decay, ema_sum[o]), __fmul_rn(omg, cs));
-            ema_sum[o] = m;
-            ev = __fdiv_rn(m, nhat);
-            E[o] = ev;
-        } else {
-            ev = E[o];
         }
-        const __nv_bfloat16 eb = __float2bfloat16_rn(ev);
-        if (E_bf16 != nullptr) E_bf16[o] = eb;
-        const float en = search == VQ_SEARCH_BF16 ? __bfloat162float(eb) : ev;
-        nrm = fmaf(en, en, nrm);
+#pragma unroll
+        for (int b = 0; b < DB; ++b) {
+            const int d = d0 + 32 * b;
+            if (d >= D) break;
+            const int64_t o = (int64_t)k * D + d;
+            float ev;
+            if (do_ema) {
+                const float c = kPeer ? cs[b] : code_sum[o];
+                const float m = __fadd_rn(__fmul_rn(decay, ema_sum[o]), __fmul_rn(omg, c));
+                ema_sum[o] = m;
+                ev = __fdiv_rn(m, nhat);
+                E[o] = ev;
+            } else {
+                ev = E[o];
+            }
+            const __nv_bfloat16 eb = __float2bfloat16_rn(ev);
+            if (E_bf16 != nullptr) E_bf16[o] = eb;
+            const float en = search == VQ_SEARCH_BF16 ? __bfloat162float(eb) : ev;
+            nrm = fmaf(en, en, nrm);
+        }
     }
     nrm = warp_sum(nrm);
     if (lane == 0) {
