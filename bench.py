@@ -107,13 +107,19 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def make_inputs(wl, rank, device, dtype=torch.bfloat16):
-    """z ~ N(0,1) seeded 1234+rank; codebook rows from the same distribution seeded 4321."""
+def make_inputs(wl, rank, device, dtype=torch.bfloat16, data="gaussian"):
+    """z ~ N(0,1) seeded 1234+rank; codebook rows from the same distribution seeded 4321.
+    data="trained": the "trained-like" set, z = E[c] + 0.1 N(0,1) with c ~ Zipf(1.1) over the K codes (skewed usage:
+    scatter contention on the hot codes, dead codes in the tail)."""
     g = torch.Generator(device="cpu").manual_seed(4321)
     E = torch.randn(wl["K"], wl["D"], generator=g)
     gz = torch.Generator(device=device).manual_seed(1234 + rank) if device != "cpu" else torch.Generator().manual_seed(1234 + rank)
-    z = torch.randn(wl["N"], wl["D"], generator=gz, device=device, dtype=torch.float32).to(dtype)
-    return z, E
+    z = torch.randn(wl["N"], wl["D"], generator=gz, device=device, dtype=torch.float32)
+    if data == "trained":
+        p = 1.0 / torch.arange(1, wl["K"] + 1, dtype=torch.float64).pow(1.1)
+        c = torch.multinomial((p / p.sum()).float().to(device), wl["N"], replacement=True, generator=gz)
+        z = E.to(device)[c] + 0.1 * z
+    return z.to(dtype), E
 
 
 def oracle_step(R, z, E, state, K):
@@ -207,7 +213,7 @@ def run_native(args, wl):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     N, K, D = wl["N"], wl["K"], wl["D"]
-    z, E = make_inputs(wl, rank, dev)
+    z, E = make_inputs(wl, rank, dev, data=args.data)
     mod = VectorQuantizer(D, K, beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5).to(dev)
     with torch.no_grad():
         mod.codebook.copy_(E); mod.ema_sum.copy_(E)
@@ -329,7 +335,8 @@ def run_native(args, wl):
     n_total = (N + n_type) * world
     line = {"metric": METRIC, "value": n_total * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic" if args.data == "gaussian" else "synthetic (trained-like: Zipf(1.1) code usage, sigma 0.1)",
             "config": {"workload": wl["desc"], "N_per_gpu": N + n_type, "K": K, "D": D, "quantizer": "ema",
                        "parallelism": f"dp{world}", "l2": "inputs larger than L2 (%.0f MB of latents per step)" % (N * D * 2 / 1e6)},
             "e2e": {"value": n_total * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (N + n_type) * D * 2,
@@ -346,6 +353,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
     ap.add_argument("--impl", choices=["native", "reference"], default="native")
+    ap.add_argument("--data", choices=["gaussian", "trained"], default="gaussian",
+                    help="synthetic latents: N(0,1) (default) or trained-like (Zipf-skewed codes + noise)")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup

@@ -76,6 +76,30 @@ def test_module_contract_on_cpu():
         VectorQuantizer(8, 8, quantizer="gumbel")
 
 
+def test_split_quantizer_and_host_entry_contract_on_cpu():
+    """Two-codebook module (BASELINE config 3) and the host-buffer entry: object contract without a GPU."""
+    from vqvae_b200 import SplitQuantizer, VectorQuantizer, extract_code_usage_from_state
+    sq = SplitQuantizer(type_dim=48, phase_dim=8, codebook_size=64, quantizer="ema")        # frl_repr_model_v1.yaml:14-15
+    assert sq.quant_type.codebook.shape == (64, 48) and sq.quant_phase.codebook.shape == (64, 8)
+    assert sq.quant_type.channel_first and sq.quant_phase.channel_first
+    sd = sq.state_dict()
+    for k in ("quant_type.codebook", "quant_phase.codebook", "quant_type.usage_total", "quant_phase.ema_sum"):
+        assert k in sd
+    assert extract_code_usage_from_state(sd, prefix="quant_phase.").shape == (64,)
+    sq2 = SplitQuantizer(48, 8, 64, quantizer="ema")
+    sq2.load_state_dict(sd)
+    assert torch.equal(sq2.quant_type.codebook, sq.quant_type.codebook)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        sq(torch.randn(1, 48, 4, 4), torch.randn(1, 8, 2, 4, 4))
+    # the pipelined host entry refuses to run without a device: no CPU fallback anywhere on the path
+    vq = VectorQuantizer(16, 32, quantizer="ema")
+    with pytest.raises(RuntimeError, match="CUDA"):
+        vq.forward_host(torch.randn(10, 16))
+    with pytest.raises(ValueError):
+        vq.forward_host(torch.randn(10, 15))
+    assert vq.cuda_graph and vq.graph_launches == 0 and not vq._graphs
+
+
 def test_shard_bounds_cover_rows():
     from vqvae_b200.parallel import shard_bounds
     for n in (0, 1, 7, 4096, 4099):

@@ -1,5 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29533 tools/dp_check.py --quick 2>&1 | grep -v "^\*\|^W\|OMP_NUM\|^$" | tail -n 8
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus 8 --steps 30 --warmup 5 > gpurun_out/bench8_c2.log 2>&1; echo "exit $?" >> gpurun_out/bench8_c2.log
-tail -n 2 gpurun_out/bench8_c2.log | cut -c1-330
+timeout 600 python -m pytest tests/test_gpu_4_configs.py -q -x --timeout=300 2>&1 | tail -n 2
+for w in c2 c4; do
+timeout 300 python bench.py --skip-cpu --steps 30 --workload $w --data trained > gpurun_out/bench_${w}_trained.log 2>&1; echo "exit $?" >> gpurun_out/bench_${w}_trained.log
+tail -n 2 gpurun_out/bench_${w}_trained.log | grep -o '"value": [0-9.]*\|"ms_per_step": [0-9.]*\|"frac": [0-9.]*\|exit [0-9]*' | tr '\n' ' '; echo
+done

@@ -333,13 +333,23 @@ class VectorQuantizer(nn.Module):
                 self._graphs[key] = "seen"
             else:
                 if ent == "seen":
-                    ent = self._capture_step(z2, search)
-                    self._graphs[key] = ent
-                g, sz, sq_, si32, si64, ssq, code_sum, n_launch = ent
-                sz.copy_(z2)
-                g.replay()
-                self.graph_launches += n_launch
-                return sq_.clone(), ssq.clone(), si64.clone(), code_sum
+                    try:
+                        ent = self._capture_step(z2, search)
+                    except Exception as exc:        # capture refused (exotic context): stay on eager launches for good
+                        import warnings
+                        warnings.warn(f"vqvae_b200: CUDA-graph capture of the quantiser step failed ({exc}); "
+                                      "continuing with eager launches")
+                        self.cuda_graph = False
+                        self._graphs.clear()
+                        ent = None
+                    else:
+                        self._graphs[key] = ent
+                if ent is not None:
+                    g, sz, sq_, si32, si64, ssq, code_sum, n_launch = ent
+                    sz.copy_(z2)
+                    g.replay()
+                    self.graph_launches += n_launch
+                    return sq_.clone(), ssq.clone(), si64.clone(), code_sum
         q = torch.empty((N, D), dtype=z2.dtype, device=dev)
         idx32 = torch.empty(N, dtype=torch.int32, device=dev)
         idx64 = torch.empty(N, dtype=torch.int64, device=dev)
