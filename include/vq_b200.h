@@ -81,11 +81,14 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
  * sums selected by stat_kind.  Rows are visited in code-sorted order (a counting sort of idx built in ws),
  * so the sums are segmented reductions in registers with one vector red per (code, 64-row slice).
  * deterministic != 0 makes the visiting order, hence every fp32 sum, run-to-run reproducible.
- * idx is in/out: rows with non-finite z are rewritten to 0, get q = E[0] and are left out of all sums. */
+ * idx is in/out: rows with non-finite z are rewritten to 0, get q = E[0] and are left out of all sums.
+ * By-products for the torch-facing module (all nullable): idx64_out [N] = the final indices widened to int64 (the
+ * `indices` the forward returns), loss_out [1] = sq_err_sum * loss_scale (loss_scale = (1+beta)/(N*D) or beta/(N*D)). */
 int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx,
                               const float* E_f32, int K, void* q_out, int out_dtype, int64_t ldq, float* sq_err_sum,
                               float* code_cnt /* [K] or NULL */, float* code_sum /* [K*D] or NULL */, int stat_kind,
-                              int deterministic, void* ws, vq_stream_t stream);
+                              int deterministic, int64_t* idx64_out, float* loss_out, float loss_scale, void* ws,
+                              vq_stream_t stream);
 
 /* a-7..a-9 (after the cross-GPU reduce of code_cnt/code_sum, a-6):
  *   n_k <- g n_k + (1-g) cnt_k ; m_k <- g m_k + (1-g) sum_k ; n^_k = (n_k+eps)/(sum n + K eps) * sum n ;

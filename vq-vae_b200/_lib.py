@@ -31,7 +31,8 @@ SIGNATURES = {
     "vq_workspace_bytes": (_i, [_i64, _i, _i, _i, C.POINTER(C.c_size_t)]),
     "vq_prepare_codebook": (_i, [_p, _i, _i, _i, _p, _p, _p]),
     "vq_assign": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _p, _i, _i, _p, _p, _p, _p]),
-    "vq_gather_st_loss_scatter": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _i, _p, _i, _i64, _p, _p, _p, _i, _i, _p, _p]),
+    "vq_gather_st_loss_scatter": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _i, _p, _i, _i64, _p, _p, _p, _i, _i, _p, _p, _f,
+                                       _p, _p]),
     "vq_ema_update": (_i, [_p, _p, _p, _p, _p, _i, _i, _f, _f, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i, _p, _p]),
     "vq_backward": (_i, [_p, _p, _p, _i64, _i, _i64, _p, _f, _p, _i, _p]),
     "vq_codebook_grad": (_i, [_p, _i, _i, _p, _f, _p, _p]),

@@ -108,16 +108,17 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
 
 int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx,
                               const float* E_f32, int K, void* q_out, int out_dtype, int64_t ldq, float* sq_err_sum,
-                              float* code_cnt, float* code_sum, int stat_kind, int deterministic, void* ws,
-                              vq_stream_t stream) {
+                              float* code_cnt, float* code_sum, int stat_kind, int deterministic,
+                              int64_t* idx64_out, float* loss_out, float loss_scale, void* ws, vq_stream_t stream) {
     VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_gather_st_loss_scatter: bad in_dtype %d", in_dtype);
     VQ_REQUIRE(out_dtype == in_dtype, "vq_gather_st_loss_scatter: out_dtype must equal in_dtype");
     VQ_REQUIRE((stat_kind & ~VQ_STAT_ACCUMULATE) == VQ_STAT_SUM_Z || (stat_kind & ~VQ_STAT_ACCUMULATE) == VQ_STAT_SUM_RESID,
                "bad stat_kind %d", stat_kind);
     VQ_REQUIRE(E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (idx != nullptr && z != nullptr && q_out != nullptr)),
                "vq_gather_st_loss_scatter: NULL argument");
+    const PassExtra extra{idx64_out, loss_out, loss_scale};
     return launch_gather_pass(z, in_dtype, N, D, ldz, idx, E_f32, K, q_out, ldq, sq_err_sum, code_cnt, code_sum,
-                              stat_kind, deterministic, ws, stream);
+                              stat_kind, deterministic, extra, ws, stream);
 }
 
 int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* code_cnt, const float* code_sum, int K,

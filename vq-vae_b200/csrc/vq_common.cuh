@@ -58,9 +58,15 @@ struct WsLayout {
     int rows_per_chunk, nchunks;
 };
 WsLayout ws_layout(int64_t N, int K, int D, int in_dtype);
+// optional by-products of the gather pass: the indices widened to int64 (the torch-facing dtype) and the scaled loss
+struct PassExtra {
+    int64_t* idx64;      // [N] or NULL
+    float* loss_out;     // [1] or NULL: sq_err_sum (after this call) * loss_scale
+    float loss_scale;
+};
 int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx, const float* E_f32,
                        int K, void* q_out, int64_t ldq, float* sq_err_sum, float* code_cnt, float* code_sum,
-                       int stat_kind, int deterministic, void* ws, cudaStream_t st);
+                       int stat_kind, int deterministic, PassExtra extra, void* ws, cudaStream_t st);
 
 }  // namespace vq
 

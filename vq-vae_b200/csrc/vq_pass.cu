@@ -314,7 +314,8 @@ __global__ void __launch_bounds__(256)
 pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
             const int32_t* __restrict__ perm, const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
             float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
-            float* __restrict__ dpart, int stat_kind, int* __restrict__ done, float* __restrict__ sq_err_out) {
+            float* __restrict__ dpart, int stat_kind, int* __restrict__ done, float* __restrict__ sq_err_out,
+            const PassExtra X) {
     using IO = VecIO<T>;
     constexpr int EPV = IO::EPV;
     constexpr int G = 32 / LPR;
@@ -471,6 +472,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
                         }
                     }
                     ++cnt;
+                    if (X.idx64 != nullptr && lg == 0) X.idx64[r] = c;
                 } else {
                     // non-finite latent row: idx := 0, q := E[0], no contribution to loss or statistics
 #pragma unroll
@@ -483,7 +485,10 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
                             st_stream_16(q + (int64_t)r * ldq + v * EPV, IO::pack(e0));
                         }
                     }
-                    if (lg == 0) idx[r] = 0;
+                    if (lg == 0) {
+                        idx[r] = 0;
+                        if (X.idx64 != nullptr) X.idx64[r] = 0;
+                    }
                 }
             }
         }
@@ -513,7 +518,9 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
             double tot = 0.0;
 #pragma unroll
             for (int i = 0; i < 8; ++i) tot += red[i];
-            sq_err_out[0] = (stat_kind & VQ_STAT_ACCUMULATE) ? sq_err_out[0] + (float)tot : (float)tot;
+            const float total = (stat_kind & VQ_STAT_ACCUMULATE) ? sq_err_out[0] + (float)tot : (float)tot;
+            sq_err_out[0] = total;
+            if (X.loss_out != nullptr) X.loss_out[0] = total * X.loss_scale;
             *done = 0;
         }
     }
@@ -525,7 +532,7 @@ __global__ void __launch_bounds__(256)
 pass_generic_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
                     const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
                     float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
-                    int stat_kind) {
+                    int stat_kind, const PassExtra X) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     float loss = 0.f;
@@ -542,6 +549,7 @@ pass_generic_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int3
             c = 0;
             if (lane == 0) idx[row] = 0;
         }
+        if (X.idx64 != nullptr && lane == 0) X.idx64[row] = c;
         for (int d = lane; d < D; d += 32) {
             const float ev = E[(int64_t)c * D + d];
             q[row * ldq + d] = (T)ev;
@@ -576,7 +584,8 @@ reduce_dpart_kernel(const float* __restrict__ dpart, const int* __restrict__ sta
 
 // fixed-order reduction of the per-warp partial sums (double accumulate) -> out[0]
 __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ part, int64_t n,
-                                                               float* __restrict__ out, int accumulate) {
+                                                               float* __restrict__ out, int accumulate,
+                                                               const PassExtra X) {
     __shared__ double sh[32];
     double s = 0.0;
     for (int64_t i = threadIdx.x; i < n; i += 1024) s += (double)part[i];
@@ -588,14 +597,18 @@ __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __re
         s = sh[threadIdx.x];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (threadIdx.x == 0) out[0] = accumulate ? out[0] + (float)s : (float)s;
+        if (threadIdx.x == 0) {
+            const float total = accumulate ? out[0] + (float)s : (float)s;
+            out[0] = total;
+            if (X.loss_out != nullptr) X.loss_out[0] = total * X.loss_scale;
+        }
     }
 }
 
 template <typename T, int VPL, int LPR>
 int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm, const float* E,
                   int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt, float* code_sum,
-                  float* dpart, int stat_kind, int* done, float* sq_err, cudaStream_t st) {
+                  float* dpart, int stat_kind, int* done, float* sq_err, PassExtra X, cudaStream_t st) {
     constexpr int G = 32 / LPR;
     const int64_t groups = ceil_div64(N, LG);
     const int64_t warps = ceil_div64(groups, G);
@@ -611,16 +624,17 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     }
     pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, smem, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
                                                               static_cast<T*>(q), ldq, part, code_cnt, code_sum,
-                                                              dpart, stat_kind, done, sq_err);
+                                                              dpart, stat_kind, done, sq_err, X);
     return VQ_OK;
 }
 
 template <typename T>
 int launch_pass_dispatch(int V, const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, const int32_t* perm,
                          const float* E, int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt,
-                         float* code_sum, float* dpart, int stat_kind, int* done, float* sq_err, cudaStream_t st) {
+                         float* code_sum, float* dpart, int stat_kind, int* done, float* sq_err, PassExtra X,
+                         cudaStream_t st) {
 #define VQ_PASS(VPL, LPR) \
-    return launch_pass_t<T, VPL, LPR>(z, N, D, ldz, idx, perm, E, K, q, ldq, part, nparts, code_cnt, code_sum, dpart, stat_kind, done, sq_err, st)
+    return launch_pass_t<T, VPL, LPR>(z, N, D, ldz, idx, perm, E, K, q, ldq, part, nparts, code_cnt, code_sum, dpart, stat_kind, done, sq_err, X, st)
     if (V <= 4) VQ_PASS(1, 4);
     if (V <= 8) VQ_PASS(1, 8);
     if (V <= 16) VQ_PASS(1, 16);
@@ -656,7 +670,7 @@ WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
 
 int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx, const float* E_f32,
                        int K, void* q_out, int64_t ldq, float* sq_err_sum, float* code_cnt, float* code_sum,
-                       int stat_kind, int deterministic, void* ws, cudaStream_t st) {
+                       int stat_kind, int deterministic, PassExtra X, void* ws, cudaStream_t st) {
     VQ_REQUIRE(N >= 0 && N < (int64_t(1) << 31) && D > 0 && K > 0 && ldz >= D && ldq >= D,
                "vq_gather_st_loss_scatter: bad shape N=%lld D=%d K=%d", (long long)N, D, K);
     VQ_REQUIRE((code_cnt == nullptr) == (code_sum == nullptr), "code_cnt and code_sum must both be given or both NULL");
@@ -664,6 +678,7 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     const bool accum = (stat_kind & VQ_STAT_ACCUMULATE) != 0;    // add to code_cnt / code_sum / sq_err_sum instead of overwriting
     if (N == 0) {
         if (accum) return VQ_OK;
+        if (X.loss_out != nullptr) VQ_CHECK_CUDA(cudaMemsetAsync(X.loss_out, 0, 4, st));
         if (stats) {
             VQ_CHECK_CUDA(cudaMemsetAsync(code_cnt, 0, (size_t)K * 4, st));
             VQ_CHECK_CUDA(cudaMemsetAsync(code_sum, 0, (size_t)K * D * 4, st));
@@ -701,11 +716,11 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         if (in_dtype == VQ_DT_F32)
             pass_generic_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const float*>(z), N, D, ldz, idx,
                                                                          E_f32, K, static_cast<float*>(q_out), ldq,
-                                                                         part, code_cnt, code_sum, stat_kind);
+                                                                         part, code_cnt, code_sum, stat_kind, X);
         else
             pass_generic_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(
                 static_cast<const __nv_bfloat16*>(z), N, D, ldz, idx, E_f32, K, static_cast<__nv_bfloat16*>(q_out), ldq,
-                part, code_cnt, code_sum, stat_kind);
+                part, code_cnt, code_sum, stat_kind, X);
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
     } else {
@@ -759,10 +774,10 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         const int V = D / epv;
         if (in_dtype == VQ_DT_F32)
             launch_pass_dispatch<float>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts, code_cnt,
-                                        code_sum, dpart, stat_kind, done, sq_err_sum, st);
+                                        code_sum, dpart, stat_kind, done, sq_err_sum, X, st);
         else
             launch_pass_dispatch<__nv_bfloat16>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts,
-                                                code_cnt, code_sum, dpart, stat_kind, done, sq_err_sum, st);
+                                                code_cnt, code_sum, dpart, stat_kind, done, sq_err_sum, X, st);
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
         if (dpart != nullptr) {
@@ -772,7 +787,7 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         }
         return VQ_OK;                       // sq_err_sum was written by the pass kernel's last block
     }
-    reduce_partials_kernel<<<1, 1024, 0, st>>>(part, nparts, sq_err_sum, accum ? 1 : 0);
+    reduce_partials_kernel<<<1, 1024, 0, st>>>(part, nparts, sq_err_sum, accum ? 1 : 0, X);
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

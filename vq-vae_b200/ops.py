@@ -87,9 +87,14 @@ def assign(z: torch.Tensor, E: torch.Tensor, E_bf16: Optional[torch.Tensor], e_n
 def gather_st_loss_scatter(z: torch.Tensor, idx: torch.Tensor, E: torch.Tensor, q_out: torch.Tensor,
                            sq_err_sum: torch.Tensor, code_cnt: Optional[torch.Tensor],
                            code_sum: Optional[torch.Tensor], stat_kind: int, deterministic: bool,
-                           ws: Optional[torch.Tensor], accumulate: bool = False) -> None:
-    """accumulate: add to sq_err_sum / code_cnt / code_sum instead of overwriting (row chunks of one batch)."""
-    _need_cuda(z, idx, E, q_out, sq_err_sum, code_cnt, code_sum, ws)
+                           ws: Optional[torch.Tensor], accumulate: bool = False, idx64_out: Optional[torch.Tensor] = None,
+                           loss_out: Optional[torch.Tensor] = None, loss_scale: float = 0.0) -> None:
+    """accumulate: add to sq_err_sum / code_cnt / code_sum instead of overwriting (row chunks of one batch).
+    idx64_out [N] int64 / loss_out [1] fp32 (optional): the final indices widened to int64 and sq_err_sum * loss_scale,
+    written by the pass itself (no torch elementwise kernels on the path)."""
+    _need_cuda(z, idx, E, q_out, sq_err_sum, code_cnt, code_sum, ws, idx64_out, loss_out)
+    assert idx64_out is None or (idx64_out.dtype == torch.int64 and idx64_out.is_contiguous() and idx64_out.numel() >= z.shape[0])
+    assert loss_out is None or loss_out.dtype == torch.float32
     if accumulate:
         stat_kind |= _lib.VQ_STAT_ACCUMULATE
     N, D, ld = _rows(z)
@@ -99,7 +104,8 @@ def gather_st_loss_scatter(z: torch.Tensor, idx: torch.Tensor, E: torch.Tensor, 
     assert idx.dtype == torch.int32 and E.dtype == torch.float32 and E.is_contiguous()
     check(_lib.load().vq_gather_st_loss_scatter(_ptr(z), _dt(z), N, D, ld, _ptr(idx), _ptr(E), K, _ptr(q_out),
                                                 _dt(q_out), ldq, _ptr(sq_err_sum), _ptr(code_cnt), _ptr(code_sum),
-                                                stat_kind, int(bool(deterministic)), _ptr(ws), _stream()),
+                                                stat_kind, int(bool(deterministic)), _ptr(idx64_out), _ptr(loss_out),
+                                                float(loss_scale), _ptr(ws), _stream()),
           "vq_gather_st_loss_scatter")
 
 

@@ -80,9 +80,8 @@ class _VQFunction(torch.autograd.Function):
         K = mod.codebook_size
         search = mod._search_for(z2.dtype)
         mod._ensure_shadow(search)
-        q, sqerr, idx, code_sum = mod._run_step(z2, search)
-        w = (1.0 + mod.beta) if mod.quantizer == "st" else mod.beta
-        loss = (sqerr * (w / float(max(N * D, 1)))).reshape(())
+        q, loss, idx, code_sum = mod._run_step(z2, search)
+        loss = loss.reshape(())
         ctx.save_for_backward(z2, q)
         ctx.mod, ctx.N, ctx.D = mod, N, D
         ctx.resid = code_sum.clone() if (mod.quantizer == "st" and codebook.requires_grad) else None
@@ -294,8 +293,13 @@ class VectorQuantizer(nn.Module):
         return self.sync_stats and parallel.dist_active(self.process_group)
 
     # ------------------------------------------------------------------ one step of kernels (eager or as a CUDA graph)
-    def _step_kernels(self, z2, q, idx32, idx64, sqerr, search: str):
-        """a-1 .. a-9 on preallocated tensors; every launch goes to the current stream (capturable)."""
+    def _loss_scale(self, N: int) -> float:
+        w = (1.0 + self.beta) if self.quantizer == "st" else self.beta
+        return w / float(max(N * self.emb_dim, 1))
+
+    def _step_kernels(self, z2, q, idx32, idx64, sqerr, loss, search: str):
+        """a-1 .. a-9 on preallocated tensors; every launch goes to the current stream (capturable).  The int64 indices
+        and the scaled loss are by-products of the gather pass: no torch arithmetic on the path."""
         N, D = z2.shape
         K = self.codebook_size
         ws = self._workspace(N, z2.dtype)
@@ -304,9 +308,9 @@ class VectorQuantizer(nn.Module):
         E = self.codebook.detach()
         ops.assign(z2, E, self._E_bf16, self._e_norm2, search, idx32, None, ws)
         kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
-        ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws)
+        ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws,
+                                   idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N))
         self._finish_step(code_cnt, code_sum, search, ws)
-        idx64.copy_(idx32)
         return code_sum
 
     def _graph_wanted(self, z2) -> bool:
@@ -322,7 +326,8 @@ class VectorQuantizer(nn.Module):
         if self._graph_wanted(z2):
             # every address the captured launches hold is part of the key: a moved module, a regrown workspace or a
             # re-created shadow simply never matches the stale entry again
-            key = (N, z2.dtype, search, self.training, self.quantizer, self.deterministic, self.codebook.data_ptr(),
+            key = (N, z2.dtype, search, self.training, self.quantizer, self.deterministic, self.beta, self.ema_decay,
+                   self.ema_eps, self.dead_after, self.codebook.data_ptr(),
                    self.ema_sum.data_ptr(), self._E_bf16.data_ptr() if self._E_bf16 is not None else 0,
                    self._e_norm2.data_ptr(), self._workspace(N, z2.dtype).data_ptr(), self._stats_buffer().data_ptr(),
                    dev.index)
@@ -345,17 +350,18 @@ class VectorQuantizer(nn.Module):
                     else:
                         self._graphs[key] = ent
                 if ent is not None:
-                    g, sz, sq_, si32, si64, ssq, code_sum, n_launch = ent
+                    g, sz, sq_, si32, si64, ssq, sloss, code_sum, n_launch = ent
                     sz.copy_(z2)
                     g.replay()
                     self.graph_launches += n_launch
-                    return sq_.clone(), ssq.clone(), si64.clone(), code_sum
+                    return sq_.clone(), sloss.clone(), si64.clone(), code_sum
         q = torch.empty((N, D), dtype=z2.dtype, device=dev)
         idx32 = torch.empty(N, dtype=torch.int32, device=dev)
         idx64 = torch.empty(N, dtype=torch.int64, device=dev)
         sqerr = torch.empty(1, dtype=torch.float32, device=dev)
-        code_sum = self._step_kernels(z2, q, idx32, idx64, sqerr, search)
-        return q, sqerr, idx64, code_sum
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        code_sum = self._step_kernels(z2, q, idx32, idx64, sqerr, loss, search)
+        return q, loss, idx64, code_sum
 
     def _capture_step(self, z2, search: str):
         N, D = z2.shape
@@ -365,14 +371,18 @@ class VectorQuantizer(nn.Module):
         si32 = torch.empty(N, dtype=torch.int32, device=dev)
         si64 = torch.empty(N, dtype=torch.int64, device=dev)
         ssq = torch.empty(1, dtype=torch.float32, device=dev)
+        sloss = torch.empty(1, dtype=torch.float32, device=dev)
         self._workspace(N, z2.dtype)                 # sized before capture: the graph holds its address
         self._stats_buffer()
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize(dev)
         l0 = ops.launch_count()
-        with torch.cuda.graph(g):                    # records, does not execute: module state is untouched
-            code_sum = self._step_kernels(sz, sq_, si32, si64, ssq, search)
-        return (g, sz, sq_, si32, si64, ssq, code_sum, ops.launch_count() - l0)
+        # records, does not execute: module state is untouched.  "relaxed": nothing is allocated or synchronised between
+        # begin and end of the capture here, and event queries made meanwhile by the caching allocators (record_stream'd
+        # tensors, a DataLoader's pin-memory thread) must not invalidate it
+        with torch.cuda.graph(g, capture_error_mode="relaxed"):
+            code_sum = self._step_kernels(sz, sq_, si32, si64, ssq, sloss, search)
+        return (g, sz, sq_, si32, si64, ssq, sloss, code_sum, ops.launch_count() - l0)
 
     # ------------------------------------------------------------------ a-6 .. a-9
     def _finish_step(self, code_cnt, code_sum, search: str, ws) -> None:
@@ -458,7 +468,9 @@ class VectorQuantizer(nn.Module):
         z_dev = torch.empty((N, D), dtype=zh.dtype, device=dev)
         q = torch.empty((N, D), dtype=zh.dtype, device=dev)
         idx32 = torch.empty(N, dtype=torch.int32, device=dev)
+        idx64 = torch.empty(N, dtype=torch.int64, device=dev)
         sqerr = torch.zeros(1, dtype=torch.float32, device=dev)
+        loss = torch.zeros(1, dtype=torch.float32, device=dev)
         stats = self._stats_buffer()
         code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
         ws = self._workspace(rows if N > 0 else 0, zh.dtype)
@@ -476,16 +488,16 @@ class VectorQuantizer(nn.Module):
             cur.wait_event(landed[c])
             ops.assign(z_dev[a:b], E, self._E_bf16, self._e_norm2, search, idx32[a:b], None, ws)
             ops.gather_st_loss_scatter(z_dev[a:b], idx32[a:b], E, q[a:b], sqerr, code_cnt, code_sum, kind,
-                                       self.deterministic, ws, accumulate=c > 0)
+                                       self.deterministic, ws, accumulate=c > 0, idx64_out=idx64[a:b], loss_out=loss,
+                                       loss_scale=self._loss_scale(N))
         if not bounds:
-            ops.gather_st_loss_scatter(z_dev, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws)
+            ops.gather_st_loss_scatter(z_dev, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws,
+                                       idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N))
         z_dev.record_stream(copy)
-        w = (1.0 + self.beta) if self.quantizer == "st" else self.beta
-        loss = (sqerr * (w / float(max(N * D, 1)))).reshape(())
         self._finish_step(code_cnt, code_sum, search, ws)
         if q.dtype != z_host.dtype:
             q = q.to(z_host.dtype)
-        return q.reshape(*lead, D), loss, idx32.to(torch.int64).reshape(lead)
+        return q.reshape(*lead, D), loss.reshape(()), idx64.reshape(lead)
 
     def _forward_channel_first(self, z: torch.Tensor):
         if z.dim() < 2 or z.shape[1] != self.emb_dim:
