@@ -203,3 +203,21 @@ def test_cuda_graph_replay_equals_eager(quantizer, dtype):
         assert torch.equal(a.last_perplexity, b.last_perplexity) and torch.equal(a.ema_sum, b.ema_sum)
     assert any(not isinstance(v, str) for v in a._graphs.values())      # a graph was really captured and replayed
     assert not b._graphs
+
+
+def test_split_quantizer_forward_host_equals_forward():
+    from vqvae_b200 import SplitQuantizer
+    torch.manual_seed(10)
+    D, K = 64, 256
+    a = SplitQuantizer(D, D, K, channel_first=False, quantizer="ema", deterministic=True).cuda()
+    b = SplitQuantizer(D, D, K, channel_first=False, quantizer="ema", deterministic=True).cuda()
+    b.load_state_dict(a.state_dict())
+    zt = torch.randn(40000, D).to(torch.bfloat16).pin_memory()
+    zp = torch.randn(150000, D).to(torch.bfloat16).pin_memory()
+    with torch.no_grad():
+        (qa_t, _, ia_t), (qa_p, _, ia_p) = a(zt.cuda(), zp.cuda())
+    (qb_t, _, ib_t), (qb_p, _, ib_p) = b.forward_host(zt, zp)
+    torch.cuda.synchronize()
+    assert torch.equal(ia_t, ib_t) and torch.equal(ia_p, ib_p) and torch.equal(qa_t, qb_t) and torch.equal(qa_p, qb_p)
+    np.testing.assert_allclose(float(b.loss), float(a.loss), rtol=1e-5)
+    np.testing.assert_allclose(b.quant_phase.codebook.cpu().numpy(), a.quant_phase.codebook.cpu().numpy(), rtol=2e-5, atol=1e-6)

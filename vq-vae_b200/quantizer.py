@@ -539,6 +539,16 @@ class SplitQuantizer(nn.Module):
     def perplexity(self) -> dict:
         return {"type": self.quant_type.perplexity, "phase": self.quant_phase.perplexity}
 
+    @torch.no_grad()
+    def forward_host(self, z_type_host: torch.Tensor, z_phase_host: torch.Tensor):
+        """Both streams from (pinned) host memory, channel-last rows: each goes through its quantiser's pipelined
+        `forward_host` (copy of chunk c + 1 under the kernels of chunk c); the phase stream's copies start while the
+        type stream's last chunk is still being quantised."""
+        out_t = self.quant_type.forward_host(z_type_host)
+        out_p = self.quant_phase.forward_host(z_phase_host)
+        self.loss = out_t[1] + out_p[1]
+        return out_t, out_p
+
     def forward(self, z_type: torch.Tensor, z_phase: torch.Tensor):
         if not (z_type.is_cuda and z_phase.is_cuda):
             raise RuntimeError("SplitQuantizer.forward needs CUDA tensors (no CPU fallback)")
