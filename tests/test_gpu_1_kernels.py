@@ -98,8 +98,8 @@ def test_nonfinite_rows():
     E = torch.randn(32, 16, generator=g)
     z = torch.randn(500, 16, generator=g)
     z[3, 2] = float("nan"); z[77, 0] = float("inf"); z[499, 15] = float("-inf")
-    for dt in (torch.float32, torch.bfloat16):
-        rep, out = check_step_against_oracle(z, E, "fp32", dt)
+    for search, dt in (("fp32", torch.float32), ("fp32", torch.bfloat16), ("bf16", torch.bfloat16), ("bf16", torch.float32)):
+        rep, out = check_step_against_oracle(z, E, search, dt)       # "bf16": the tcgen05 CTA-pair search sees NaN / inf rows
         assert out["idx"][3] == 0 and out["idx"][77] == 0 and out["idx"][499] == 0
         assert torch.isfinite(out["sqerr"])
 
