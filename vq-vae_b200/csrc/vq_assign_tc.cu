@@ -2,18 +2,19 @@
 //
 //   idx[n] = argmin_k ( ||e_k||^2 - 2 z_n . e_k )        z: [N, D] bf16,  E: [K, D] bf16,  ||e||^2: fp32
 //
-// The N x K score matrix never exists in HBM: each CTA owns a 128-row slab of z (kept resident in shared
-// memory for the whole sweep), streams the codebook through a TMA ring in 256-code x 64-feature stages,
-// accumulates S = z E^T for one 128 x 256 tile in TMEM (fp32), and the epilogue warps fold each finished tile
-// into a running (min, argmin) per row straight out of TMEM while the tensor core works on the next tile
-// (two accumulator buffers = all 512 TMEM columns).
+// The N x K score matrix never exists in HBM: a CTA pair (two SMs of a TPC, tcgen05 cta_group::2) owns a 256-row slab
+// of z, 128 rows per CTA, kept resident in shared memory for the whole sweep; the codebook streams through a TMA ring in
+// 256-code x 64-feature stages of which each CTA holds 128 codes; S = z E^T accumulates for one 256 x 256 tile in the
+// TMEM of both SMs (fp32, 128 rows each), and the epilogue warps fold each finished tile into a running (min, argmin)
+// per row straight out of TMEM while the tensor cores work on the next tile (two accumulator buffers = all 512 TMEM
+// columns).  kPair = false is the same kernel on single CTAs (cta_group::1, 128-row slabs, whole stages per CTA).
 //
-// Warp roles (384 threads, 1 CTA / SM, persistent over row slabs):
-//   warp 0      TMA producer (one elected lane)
-//   warp 1      tcgen05.mma issuer (one elected lane)
+// Warp roles (128 + 32 * kEpiWarps threads, 1 CTA / SM, persistent over row slabs):
+//   warp 0      TMA producer (one elected lane; in a pair both CTAs load, completion goes to the leader's barriers)
+//   warp 1      tcgen05.mma issuer (one elected lane; in a pair the leader CTA only)
 //   warp 2      TMEM allocator / deallocator
-//   warps 4-11  epilogue: warp w reads TMEM lanes 32*(w%4)..+31 (one row per thread), columns
-//               [128*((w-4)/4), +128) of each tile; the two halves are merged through smem per slab.
+//   warps 4..   epilogue (8 warps in pairs, 16 on single CTAs): warp w reads TMEM lanes 32*(w%4)..+31 (one row per
+//               thread) and one column part of each tile; the parts are merged through shared memory per slab.
 //
 // Required by: scripts/train_vqvae.py:11,287 (VectorQuantizer inside model(batch));
 //              frl/config/frl_model_v0.yaml:29-33 (kind: vq, K, D).  Definition: SURVEY.md 8(a-1).
