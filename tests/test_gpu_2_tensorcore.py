@@ -17,6 +17,7 @@ pytestmark = pytest.mark.gpu
     (128, 256, 64), (1, 1, 8), (127, 100, 16), (129, 255, 32), (300, 257, 64), (5000, 1000, 128),
     (4096, 1024, 128), (2000, 512, 72), (1500, 3000, 256), (777, 513, 512), (148 * 128 * 2 + 77, 512, 64),
     (3000, 8192, 256), (2048, 2048, 48), (1000, 2048, 8),      # last two: the live model's z_type_dim / z_phase_dim (frl_repr_model_v1.yaml:14-15)
+    (6000, 20000, 64),      # K beyond the shared-memory histogram and norm staging: global-counter sort, norms from L2
 ])
 def test_tc_search_shapes(N, K, D):
     from gpu_util import check_step_against_oracle
