@@ -196,16 +196,30 @@ def test_reference_default_sizes_bf16(K, D):
 
 
 @pytest.mark.gpu
-def test_fp16_autocast_input_is_quantised_in_fp32():
-    """scripts/train_vqvae.py:284-286 runs the model under fp16 autocast unless --bf16: half latents are widened."""
+@pytest.mark.parametrize("search", ["auto", "fp32"])
+def test_fp16_autocast_input(search):
+    """scripts/train_vqvae.py:284-286 runs the model under fp16 autocast unless --bf16.  Half latents are widened to
+    fp32 for gather / loss / statistics; "auto" sends them through the tensor-core search (staged as bf16),
+    search="fp32" keeps the exact tier."""
     from vqvae_b200 import VectorQuantizer
     torch.manual_seed(5)
-    mod = VectorQuantizer(32, 64, quantizer="st").cuda()
-    z = torch.randn(4, 10, 32, device="cuda", dtype=torch.float16, requires_grad=True)
+    mod = VectorQuantizer(32, 64, quantizer="st", search=search).cuda()
+    with torch.no_grad():
+        mod.codebook.normal_()
+    z = torch.randn(4, 1000, 32, device="cuda", dtype=torch.float16, requires_grad=True)
     with torch.autocast("cuda", dtype=torch.float16):
         q, loss, idx = mod(z)
-    assert q.dtype == torch.float16 and loss.dtype == torch.float32 and idx.shape == (4, 10)
-    ref_idx, _ = R.assign(z.detach().float().cpu().reshape(-1, 32), mod.codebook.detach().cpu(), "fp32")
-    assert torch.equal(idx.cpu().reshape(-1), ref_idx)
+    assert q.dtype == torch.float16 and loss.dtype == torch.float32 and idx.shape == (4, 1000)
+    zf, E = z.detach().float().cpu().reshape(-1, 32), mod.codebook.detach().cpu()
+    if search == "fp32":
+        ref_idx, _ = R.assign(zf, E, "fp32")
+        assert torch.equal(idx.cpu().reshape(-1), ref_idx)
+    else:
+        ref_idx, _ = R.assign(zf, E, "bf16")
+        rep = R.near_tie_report(zf, E, idx.cpu().reshape(-1), ref_idx, precision="bf16")
+        assert rep["hard"] == 0, rep
+    assert torch.equal(q.detach().float().cpu().reshape(-1, 32), E[idx.cpu().reshape(-1)].to(torch.float16).float())
+    mse = float(((zf - E[idx.cpu().reshape(-1)]) ** 2).mean())
+    np.testing.assert_allclose(float(loss), 1.25 * mse, rtol=1e-4)          # loss on the exact fp32 values
     (q.float().sum() + loss).backward()
     assert torch.isfinite(z.grad).all() and mod.codebook.grad is not None

@@ -75,10 +75,9 @@ class _VQFunction(torch.autograd.Function):
     """Forward = search + fused gather pass (+ statistics); backward = straight-through + commitment."""
 
     @staticmethod
-    def forward(ctx, z2: torch.Tensor, codebook: torch.Tensor, mod: "VectorQuantizer"):
+    def forward(ctx, z2: torch.Tensor, codebook: torch.Tensor, mod: "VectorQuantizer", search: str):
         N, D = z2.shape
         K = mod.codebook_size
-        search = mod._search_for(z2.dtype)
         mod._ensure_shadow(search)
         q, loss, idx, code_sum = mod._run_step(z2, search)
         loss = loss.reshape(())
@@ -103,7 +102,7 @@ class _VQFunction(torch.autograd.Function):
         if ctx.needs_input_grad[1] and ctx.resid is not None:
             grad_E = torch.empty((mod.codebook_size, D), dtype=torch.float32, device=dev)
             ops.codebook_grad(ctx.resid, gl, 2.0 / float(max(N * D, 1)), grad_E)
-        return grad_z, grad_E, None
+        return grad_z, grad_E, None, None
 
 
 class _LayoutTranspose(torch.autograd.Function):
@@ -233,9 +232,11 @@ class VectorQuantizer(nn.Module):
 
     # ------------------------------------------------------------------ scratch management
     def _search_for(self, dtype: torch.dtype) -> str:
+        """"auto": half-precision latents (bf16, and fp16 -- the reference script's default autocast dtype,
+        scripts/train_vqvae.py:284-286) take the tensor-core search, fp32 latents the fp32 search."""
         if self.search != "auto":
             return self.search
-        return "bf16" if dtype == torch.bfloat16 else "fp32"
+        return "bf16" if dtype in (torch.bfloat16, torch.float16) else "fp32"
 
     def _ensure_shadow(self, search: str) -> None:
         """(Re)build the bf16 copy and ||e||^2 the search reads if the codebook changed behind our back
@@ -420,11 +421,14 @@ class VectorQuantizer(nn.Module):
             lead = z.shape[:-1]
             in_dtype = z.dtype
             z2 = z.reshape(-1, self.emb_dim)
+            search = self._search_for(z2.dtype)
             if z2.dtype not in (torch.bfloat16, torch.float32):
-                z2 = z2.to(torch.float32)            # fp16 autocast: quantise in fp32, cast back below
+                # fp16 autocast: gather, loss and statistics in fp32 on the widened values (cast back below); the SEARCH
+                # stages them as bf16 for the tensor core unless search="fp32" asks for the exact tier
+                z2 = z2.to(torch.float32)
             if z2.shape[0] > 1 and (z2.stride(1) != 1 or z2.stride(0) < self.emb_dim):
                 z2 = z2.contiguous()
-            q, loss, idx = _VQFunction.apply(z2, self.codebook, self)
+            q, loss, idx = _VQFunction.apply(z2, self.codebook, self, search)
             if q.dtype != in_dtype:
                 q = q.to(in_dtype)
             return q.reshape(*lead, self.emb_dim), loss, idx.reshape(lead)
@@ -443,6 +447,7 @@ class VectorQuantizer(nn.Module):
             raise ValueError("forward_host expects channel-last rows [..., D]")
         if z_host.shape[-1] != self.emb_dim:
             raise ValueError(f"last dimension {z_host.shape[-1]} != emb_dim {self.emb_dim}")
+        search = self._search_for(z_host.dtype)
         if z_host.dtype not in (torch.bfloat16, torch.float32):
             z_host = z_host.to(torch.float32)
         dev = self.codebook.device
@@ -459,7 +464,6 @@ class VectorQuantizer(nn.Module):
             chunks = max(1, min(16, N // 131072))
         rows = max(128, -(-N // max(1, chunks)) // 128 * 128) if N > 0 else 1
         bounds = [(s, min(N, s + rows)) for s in range(0, max(N, 1), rows)] if N > 0 else []
-        search = self._search_for(zh.dtype)
         self._ensure_shadow(search)
         cur = torch.cuda.current_stream(dev)
         if getattr(self, "_copy_stream", None) is None or self._copy_stream.device != dev:
@@ -506,10 +510,11 @@ class VectorQuantizer(nn.Module):
             B, D, spatial = z.shape[0], z.shape[1], z.shape[2:]
             in_dtype = z.dtype
             z3 = z.reshape(B, D, -1)
+            search = self._search_for(z3.dtype)
             if z3.dtype not in (torch.bfloat16, torch.float32):
                 z3 = z3.to(torch.float32)
             rows = _LayoutTranspose.apply(z3)                          # [B, S, D]
-            q, loss, idx = _VQFunction.apply(rows.reshape(-1, D), self.codebook, self)
+            q, loss, idx = _VQFunction.apply(rows.reshape(-1, D), self.codebook, self, search)
             qcf = _LayoutTranspose.apply(q.reshape(B, -1, D))          # [B, D, S]
             if qcf.dtype != in_dtype:
                 qcf = qcf.to(in_dtype)
