@@ -35,21 +35,31 @@ extern "C" {
 typedef struct CUstream_st* vq_stream_t; /* == cudaStream_t */
 #endif
 
-#define VQ_ABI_VERSION 1
+#define VQ_ABI_VERSION 2
 
 enum { VQ_OK = 0, VQ_ERR_ARG = 1, VQ_ERR_CUDA = 2, VQ_ERR_UNSUPPORTED = 3 };
 enum { VQ_DT_BF16 = 0, VQ_DT_F32 = 1 };
 /* arithmetic of the distance search */
 enum {
     VQ_SEARCH_BF16 = 0, /* z, E rounded to bf16, fp32 accumulate: tcgen05 tensor-core kernel            */
-    VQ_SEARCH_F32 = 1   /* fp32 FMA on the CUDA cores, the 1e-5 tier                                     */
+    VQ_SEARCH_F32 = 1,  /* fp32 FMA on the CUDA cores, the 1e-5 tier                                     */
+    VQ_SEARCH_PRESORT = 256, /* flag, OR-ed in (vq_assign only, needs ws): the search also leaves in ws the per-code
+                               histogram of idx, each row's rank inside its code and the exclusive scan, so that
+                               vq_gather_st_loss_scatter(... | VQ_STAT_PRESORTED) can skip its own histogram passes */
+    VQ_SEARCH_WS_CLEAN = 512 /* flag, with VQ_SEARCH_PRESORT: the caller guarantees that the counter region of ws is
+                               zero -- ws was zero-filled when it was allocated and, since then, only calls carrying
+                               VQ_SEARCH_PRESORT / VQ_STAT_PRESORTED have used it (those leave it zero again) -- so the
+                               search skips its memset (5-8 us in front of the kernel) */
 };
 /* what vq_gather_st_loss_scatter accumulates per code */
 enum {
     VQ_STAT_SUM_Z = 0,  /* sum_k = sum z_n         (EMA statistics, a-5)                                 */
     VQ_STAT_SUM_RESID = 1, /* sum_k = sum (z_n - e_k) (st mode: codebook gradient = -2g/(ND) * sum_k)     */
-    VQ_STAT_ACCUMULATE = 16 /* flag, OR-ed in: add to code_cnt / code_sum / sq_err_sum instead of overwriting them
+    VQ_STAT_ACCUMULATE = 16, /* flag, OR-ed in: add to code_cnt / code_sum / sq_err_sum instead of overwriting them
                                (a batch processed in row chunks, e.g. while the next chunk is still in flight) */
+    VQ_STAT_PRESORTED = 32  /* flag, OR-ed in: idx was produced by vq_assign(... | VQ_SEARCH_PRESORT) with the same
+                               N, K, D, in_dtype and ws, and neither idx nor ws has been written since: the counting
+                               sort shrinks to one scatter launch.  Ignored where the pass cannot use it. */
 };
 
 int vq_abi_version(void);

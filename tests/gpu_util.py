@@ -20,6 +20,7 @@ def cuda_step(z_cpu, E_cpu, search, dtype=torch.float32, deterministic=False, st
     ws = torch.empty(ops.workspace_bytes(N, K, D, dtype), dtype=torch.uint8, device=dev)
     idx = torch.full((N,), -1, dtype=torch.int32, device=dev)
     smin = torch.empty(N, dtype=torch.float32, device=dev) if want_smin else None
+    # (1) stand-alone calls: the pass builds its own counting sort
     ops.assign(z, E, E_bf16, norms, search, idx, smin, ws)
     raw_idx = idx.clone()
     q = torch.empty_like(z)
@@ -28,6 +29,47 @@ def cuda_step(z_cpu, E_cpu, search, dtype=torch.float32, deterministic=False, st
     sums = torch.empty((K, D), dtype=torch.float32, device=dev) if stats else None
     ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, stat_kind, deterministic, ws)
     torch.cuda.synchronize()
+    # (2) the production pairing: the search leaves histogram / ranks / scan in ws (VQ_SEARCH_PRESORT) and the pass
+    # picks them up (VQ_STAT_PRESORTED).  Must agree with (1); its results are the ones returned.
+    first = dict(idx=idx.clone(), q=q.clone(), sq=sq.clone(), cnt=None if cnt is None else cnt.clone(),
+                 sums=None if sums is None else sums.clone())
+    idx.fill_(-1)
+    q.fill_(float("nan"))
+    if stats:
+        cnt.fill_(-7.0)
+        sums.fill_(float("nan"))
+    ops.assign(z, E, E_bf16, norms, search, idx, smin, ws, presort=True)
+    assert torch.equal(idx, raw_idx), "VQ_SEARCH_PRESORT changed the indices"
+    ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, stat_kind, deterministic, ws, presorted=True)
+    torch.cuda.synchronize()
+    assert torch.equal(idx, first["idx"]) and torch.equal(q.view(torch.uint8), first["q"].view(torch.uint8))
+    sq_a, sq_b = float(first["sq"]), float(sq)
+    assert sq_a == sq_b or abs(sq_a - sq_b) <= 1e-5 * abs(sq_a), (sq_a, sq_b)
+    if stats:
+        assert torch.equal(cnt, first["cnt"]), "presorted pass: per-code counts differ"
+        fin = torch.isfinite(first["sums"])
+        assert torch.equal(fin, torch.isfinite(sums))
+        scale = first["sums"][fin].abs().max().clamp_min(1e-30) if bool(fin.any()) else 1.0
+        assert float(((sums - first["sums"])[fin].abs().max() if bool(fin.any()) else 0.0) / scale) <= 1e-5
+    # (3) the module's contract: a zero-filled workspace of its own, VQ_SEARCH_WS_CLEAN (no memset in front of the search);
+    # the search kernel's last block must leave the counters zero again, so the second round has to agree as well
+    ws3 = torch.zeros_like(ws)
+    for _ in range(2):
+        idx3 = torch.full_like(idx, -1)
+        q3 = torch.full_like(q, float("nan"))
+        sq3 = torch.empty_like(sq)
+        cnt3 = torch.full_like(cnt, -7.0) if stats else None
+        sums3 = torch.full_like(sums, float("nan")) if stats else None
+        ops.assign(z, E, E_bf16, norms, search, idx3, None, ws3, presort=True, ws_clean=True)
+        ops.gather_st_loss_scatter(z, idx3, E, q3, sq3, cnt3, sums3, stat_kind, deterministic, ws3, presorted=True)
+        torch.cuda.synchronize()
+        assert torch.equal(idx3, idx) and torch.equal(q3.view(torch.uint8), q.view(torch.uint8))
+        assert abs(float(sq3) - float(sq)) <= 1e-5 * abs(float(sq)) or float(sq3) == float(sq)
+        if stats:
+            assert torch.equal(cnt3, cnt), "ws_clean round: per-code counts differ"
+            fin = torch.isfinite(sums)
+            scale = sums[fin].abs().max().clamp_min(1e-30) if bool(fin.any()) else 1.0
+            assert float(((sums3 - sums)[fin].abs().max() if bool(fin.any()) else 0.0) / scale) <= 1e-5
     out = dict(idx=idx.cpu().long(), raw_idx=raw_idx.cpu().long(), q=q.cpu(), sqerr=sq.cpu()[0],
                norms=norms.cpu(), E_bf16=E_bf16.cpu())
     if want_smin:

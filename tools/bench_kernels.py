@@ -27,6 +27,7 @@ for name in sys.argv[1:] or ["c2", "c4"]:
     nrm = torch.empty(ops.norm_elems(K), device=dev)
     ops.prepare_codebook(E, "bf16", Eb, nrm)
     ws = torch.empty(ops.workspace_bytes(N, K, D, z.dtype), dtype=torch.uint8, device=dev)
+    wsc = torch.zeros_like(ws)              # VQ_SEARCH_WS_CLEAN contract: only presort / presorted calls touch it
     idx = torch.empty(N, dtype=torch.int32, device=dev)
     q = torch.empty_like(z)
     sq = torch.empty(1, device=dev)
@@ -36,10 +37,28 @@ for name in sys.argv[1:] or ["c2", "c4"]:
         ops.assign(z, E, Eb, nrm, "bf16", idx, None, ws)
         ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, VQ_STAT_SUM_Z, False, ws)
     torch.cuda.synchronize()
-    ta = time_kernel(lambda: ops.assign(z, E, Eb, nrm, "bf16", idx, None, ws), 10, flush)
-    tp = time_kernel(lambda: ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, VQ_STAT_SUM_Z, False, ws), 10, flush)
+    fns = [lambda: ops.assign(z, E, Eb, nrm, "bf16", idx, None, ws),
+           lambda: ops.assign(z, E, Eb, nrm, "bf16", idx, None, wsc, presort=True, ws_clean=True)]
+    evs = [[], []]
+    for _ in range(20):                      # interleaved A/B: both see the same clocks
+        for j in (0, 1):
+            flush()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fns[j](); e1.record()
+            evs[j].append((e0, e1))
+    torch.cuda.synchronize()
+    ta0, ta = (sum(a.elapsed_time(b) for a, b in ev) / len(ev) for ev in evs)
+    if os.environ.get("VQ_BENCH_SKIP_PASS"):      # timing variants whose by-products are garbage
+        print(f"{name}: assign {ta0*1e3:8.1f} us, search+presort {ta*1e3:8.1f} us", flush=True)
+        continue
+    tp0 = time_kernel(lambda: ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, VQ_STAT_SUM_Z, False, ws), 10, flush)
+    ops.assign(z, E, Eb, nrm, "bf16", idx, None, wsc, presort=True, ws_clean=True)
+    tp = time_kernel(lambda: ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, VQ_STAT_SUM_Z, False, wsc,
+                                                        presorted=True), 10, flush)
+    print(f"{name}: stand-alone calls: assign {ta0*1e3:8.1f} us, pass group {tp0*1e3:8.1f} us; "
+          f"search+presort {ta*1e3:8.1f} us, presorted pass group {tp*1e3:8.1f} us", flush=True)
     tf = 2.0 * N * K * D / (ta * 1e-3) / 1e12
-    gb = (N * (D * 4 + 4) + K * D * 8 + K * 4) / (tp * 1e-3) / 1e9
+    gb = (N * (D * 2 * z.element_size() + 4) + K * D * 8 + K * 4) / (tp * 1e-3) / 1e9
     print(f"{name}: assign {ta*1e3:8.1f} us  {tf:7.1f} TF/s ({tf/peaks['tf_burst']:.3f} of burst)   "
           f"pass group {tp*1e3:8.1f} us  {gb:7.1f} GB/s ({gb/peaks['hbm']:.3f} of hbm)  env={os.environ.get('VQ_ASSIGN_EPI_WARPS','-')}",
           flush=True)

@@ -19,14 +19,14 @@ E = E.to(dev)
 Eb = torch.empty((K, D), dtype=torch.bfloat16, device=dev)
 nrm = torch.empty(ops.norm_elems(K), device=dev)
 ops.prepare_codebook(E, "bf16", Eb, nrm)
-ws = torch.empty(ops.workspace_bytes(N, K, D, z.dtype), dtype=torch.uint8, device=dev)
+ws = torch.zeros(ops.workspace_bytes(N, K, D, z.dtype), dtype=torch.uint8, device=dev)
 idx = torch.empty(N, dtype=torch.int32, device=dev)
 q = torch.empty_like(z)
 sq = torch.empty(1, device=dev)
 cnt = torch.empty(K, device=dev)
 sums = torch.empty((K, D), device=dev)
 for _ in range(iters):
-    ops.assign(z, E, Eb, nrm, "bf16", idx, None, ws)
-    ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, VQ_STAT_SUM_Z, False, ws)
+    ops.assign(z, E, Eb, nrm, "bf16", idx, None, ws, presort=True, ws_clean=True)
+    ops.gather_st_loss_scatter(z, idx, E, q, sq, cnt, sums, VQ_STAT_SUM_Z, False, ws, presorted=True)
 torch.cuda.synchronize()
 print("ok", wl["desc"], float(sq), int(cnt.sum()))

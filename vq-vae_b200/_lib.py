@@ -17,7 +17,10 @@ VQ_DT_BF16, VQ_DT_F32 = 0, 1
 VQ_SEARCH_BF16, VQ_SEARCH_F32 = 0, 1
 VQ_STAT_SUM_Z, VQ_STAT_SUM_RESID = 0, 1
 VQ_STAT_ACCUMULATE = 16
-ABI_VERSION = 1
+VQ_STAT_PRESORTED = 32      # idx comes from vq_assign(... | VQ_SEARCH_PRESORT) on the same workspace
+VQ_SEARCH_WS_CLEAN = 512    # caller vouches that the workspace counters are zero (see include/vq_b200.h)
+VQ_SEARCH_PRESORT = 256     # vq_assign also leaves histogram / ranks / scan of idx in the workspace
+ABI_VERSION = 2
 MAX_PEERS, IPC_HANDLE_BYTES = 16, 64
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float

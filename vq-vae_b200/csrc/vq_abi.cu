@@ -81,9 +81,26 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
     if (N == 0) return VQ_OK;
     VQ_REQUIRE(idx != nullptr && e_norm2 != nullptr, "vq_assign: idx and e_norm2 are required");
     VQ_REQUIRE(z != nullptr, "vq_assign: z is NULL");
+    Presort ps{nullptr, nullptr, nullptr, nullptr};
+    const bool ws_clean = (search & VQ_SEARCH_WS_CLEAN) != 0;
+    search &= ~VQ_SEARCH_WS_CLEAN;
+    if (search & VQ_SEARCH_PRESORT) {
+        search &= ~VQ_SEARCH_PRESORT;
+        VQ_REQUIRE(ws != nullptr, "vq_assign: VQ_SEARCH_PRESORT needs the workspace");
+        VQ_REQUIRE(N < (int64_t(1) << 31), "vq_assign: VQ_SEARCH_PRESORT needs N < 2^31");
+        const WsLayout L = ws_layout(N, K, D, in_dtype);
+        uint8_t* w = static_cast<uint8_t*>(ws);
+        ps.hist = reinterpret_cast<int*>(w + L.cnt);
+        ps.rank = reinterpret_cast<int*>(w + L.rank);
+        ps.start = reinterpret_cast<int*>(w + L.start);
+        ps.done = ps.hist + 2 * K + 1;               // next to the pass kernel's own completion counter
+        // [histogram K | cursor K | pass done | search done]: one memset, unless the caller vouches for the region
+        // (the search kernel's last block re-zeroes the histogram, the completion counters reset themselves)
+        if (!ws_clean) VQ_CHECK_CUDA(cudaMemsetAsync(ps.hist, 0, (size_t)(2 * K + 2) * 4, stream));
+    }
     if (search == VQ_SEARCH_F32) {
         VQ_REQUIRE(E_f32 != nullptr, "vq_assign: E_f32 required for VQ_SEARCH_F32");
-        return launch_assign_simt(z, in_dtype, N, D, ldz, E_f32, e_norm2, K, idx, smin, stream);
+        return launch_assign_simt(z, in_dtype, N, D, ldz, E_f32, e_norm2, K, idx, smin, ps, stream);
     }
     VQ_REQUIRE(search == VQ_SEARCH_BF16, "vq_assign: bad search mode %d", search);
     VQ_REQUIRE(E_bf16 != nullptr, "vq_assign: E_bf16 required for VQ_SEARCH_BF16");
@@ -103,7 +120,7 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
                   (long long)N, D, (long long)ldb, K);
         return VQ_ERR_UNSUPPORTED;
     }
-    return launch_assign_tc(zb, N, D, ldb, E_bf16, e_norm2, K, idx, smin, stream);
+    return launch_assign_tc(zb, N, D, ldb, E_bf16, e_norm2, K, idx, smin, ps, stream);
 }
 
 int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx,
@@ -112,8 +129,10 @@ int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int
                               int64_t* idx64_out, float* loss_out, float loss_scale, void* ws, vq_stream_t stream) {
     VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_gather_st_loss_scatter: bad in_dtype %d", in_dtype);
     VQ_REQUIRE(out_dtype == in_dtype, "vq_gather_st_loss_scatter: out_dtype must equal in_dtype");
-    VQ_REQUIRE((stat_kind & ~VQ_STAT_ACCUMULATE) == VQ_STAT_SUM_Z || (stat_kind & ~VQ_STAT_ACCUMULATE) == VQ_STAT_SUM_RESID,
-               "bad stat_kind %d", stat_kind);
+    {
+        const int base_kind = stat_kind & ~(VQ_STAT_ACCUMULATE | VQ_STAT_PRESORTED);
+        VQ_REQUIRE(base_kind == VQ_STAT_SUM_Z || base_kind == VQ_STAT_SUM_RESID, "bad stat_kind %d", stat_kind);
+    }
     VQ_REQUIRE(E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (idx != nullptr && z != nullptr && q_out != nullptr)),
                "vq_gather_st_loss_scatter: NULL argument");
     const PassExtra extra{idx64_out, loss_out, loss_scale};

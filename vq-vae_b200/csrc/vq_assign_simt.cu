@@ -24,8 +24,10 @@ __device__ __forceinline__ float load_as_float<__nv_bfloat16>(const __nv_bfloat1
 template <typename T>
 __global__ void __launch_bounds__(256)
 assign_simt_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, const float* __restrict__ E,
-                   const float* __restrict__ norms, int K, int32_t* __restrict__ idx, float* __restrict__ smin) {
+                   const float* __restrict__ norms, int K, int32_t* __restrict__ idx, float* __restrict__ smin,
+                   const Presort ps) {
     __shared__ __align__(16) float zs[TK][LDS_PAD];
+    __shared__ int scan_sh[36];
     __shared__ __align__(16) float es[TK][LDS_PAD];
     const int tid = threadIdx.x;
     const int ty = tid >> 4, tx = tid & 15;
@@ -94,8 +96,10 @@ assign_simt_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, const
         if (tx == 0 && gr < N) {
             idx[gr] = bidx;
             if (smin != nullptr) smin[gr] = b;
+            if (ps.hist != nullptr) ps.rank[gr] = atomicAdd(ps.hist + bidx, 1);
         }
     }
+    if (ps.hist != nullptr) presort_finish(ps, K, scan_sh);
 }
 
 __global__ void cast_bf16_kernel(const float* __restrict__ src, int64_t N, int D, int64_t ld,
@@ -118,17 +122,17 @@ __global__ void cast_bf16_vec_kernel(const float4* __restrict__ src, int64_t n4,
 }  // namespace
 
 int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32,
-                       const float* e_norm2, int K, int32_t* idx, float* smin, cudaStream_t st) {
+                       const float* e_norm2, int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st) {
     VQ_REQUIRE(N > 0 && D > 0 && K > 0 && ldz >= D, "vq_assign(f32): bad shape N=%lld D=%d K=%d ldz=%lld",
                (long long)N, D, K, (long long)ldz);
     const int64_t grid = (N + TM - 1) / TM;
     VQ_REQUIRE(grid < (int64_t(1) << 31), "vq_assign(f32): N too large");
     if (in_dtype == VQ_DT_F32)
         assign_simt_kernel<float><<<(unsigned)grid, 256, 0, st>>>(static_cast<const float*>(z), N, D, ldz, E_f32,
-                                                                  e_norm2, K, idx, smin);
+                                                                  e_norm2, K, idx, smin, ps);
     else
         assign_simt_kernel<__nv_bfloat16><<<(unsigned)grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(z), N, D,
-                                                                          ldz, E_f32, e_norm2, K, idx, smin);
+                                                                          ldz, E_f32, e_norm2, K, idx, smin, ps);
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

@@ -47,6 +47,8 @@ struct Ctl {
     uint32_t pad;
     float xbest[2][MAX_EPI_PARTS][BM];
     int xidx[2][MAX_EPI_PARTS][BM];
+    int scan_sh[36];                   // VQ_SEARCH_PRESORT: scratch of presort_finish
+    int fin_idx[2][BM];                // VQ_SEARCH_PRESORT: a slab's final indices on their way to warp 3
 };
 
 __device__ __forceinline__ float min3f(float a, float b, float c) {
@@ -215,7 +217,8 @@ template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair>
 __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
                  const __grid_constant__ CUtensorMap tm_aug, const float* __restrict__ norms, int64_t N, int K, int D,
-                 int nkb, int nstages, int nabuf, int32_t* __restrict__ idx, float* __restrict__ smin, int dbg) {
+                 int nkb, int nstages, int nabuf, int32_t* __restrict__ idx, float* __restrict__ smin, int dbg,
+                 const Presort ps) {
     constexpr int B_ROWS = kPair ? BN / 2 : BN;          // codes of a stage held by this CTA
     constexpr int B_ST = B_ROWS * BK * 2;                // ring slot bytes (16 KiB / 32 KiB)
     extern __shared__ uint8_t smem_raw[];
@@ -408,8 +411,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                 else mbar_arrive(&ctl->t_empty[acc]);
             }
         };
-        uint32_t it = 0, xb = 0;
-        for (int64_t tile = unit; tile < ntiles; tile += nunits, xb ^= 1) {
+        // VQ_SEARCH_PRESORT: the histogram claim of a slab's rows is issued when the slab ends and consumed one slab later,
+        // so the atomic's round trip to L2 never stalls the fold of the next accumulators
+        uint32_t it = 0, xb = 0, slab_no = 0;
+        for (int64_t tile = unit; tile < ntiles; tile += nunits, xb ^= 1, ++slab_no) {
             float best = kMode == 3 ? -CUDART_INF_F : CUDART_INF_F;      // kMode 3 tracks a maximum
             int bi = 0;
             for (int nb = 0; nb < num_nb; ++nb, ++it) {
@@ -470,9 +475,40 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     idx[row] = bi;
                     if (smin != nullptr) smin[row] = best;
                 }
+                if (ps.hist != nullptr) {
+                    // hand the slab's indices to warp 3 (histogram claims + ranks): issued from here, the 32-address
+                    // atomics cost the search 5 % at D=128 although nothing waits for their results
+                    if (slab_no >= 2) named_bar_sync(4 + xb, 160);        // warp 3 has read this buffer's previous slab
+                    ctl->fin_idx[xb][rl] = row < N ? bi : -1;
+                    __threadfence_block();
+                    named_bar_arrive(2 + xb, 160);
+                }
             }
         }
+    } else if (warp == 3 && ps.hist != nullptr) {
+        // ------------------------------------------------------------------ VQ_SEARCH_PRESORT: claims and ranks
+        // Plain per-lane claims (MATCH-based aggregation costs more than it saves when K codes spread over 32 rows;
+        // same-address lanes serialise in L2 instead).  Nothing else waits for this warp.
+        uint32_t xb = 0;
+        for (int64_t tile = unit; tile < ntiles; tile += nunits, xb ^= 1) {
+            named_bar_sync(2 + xb, 160);
+            int c[4], r[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) c[j] = ctl->fin_idx[xb][j * 32 + lane];
+            __threadfence_block();
+            named_bar_arrive(4 + xb, 160);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) r[j] = c[j] >= 0 ? atomicAdd(ps.hist + c[j], 1) : 0;
+            const int64_t row0 = tile * SLAB + rank * BM + lane;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (c[j] >= 0) ps.rank[row0 + j * 32] = r[j];
+        }
     }
+
+#ifndef VQ_PRESORT_NO_FINISH
+    if (ps.hist != nullptr) presort_finish(ps, K, ctl->scan_sh);
+#endif
 
     tc_fence_before();
     __syncthreads();
@@ -552,7 +588,7 @@ bool assign_tc_supported(int64_t N, int D, int64_t ldz, int K) {
 }
 
 int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const void* E_bf16, const float* e_norm2,
-                     int K, int32_t* idx, float* smin, cudaStream_t st) {
+                     int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st) {
     VQ_REQUIRE(assign_tc_supported(N, D, ldz, K), "vq_assign(bf16): unsupported shape N=%lld D=%d ldz=%lld K=%d",
                (long long)N, D, (long long)ldz, K);
     VQ_REQUIRE((reinterpret_cast<uintptr_t>(z_bf16) & 15) == 0 && (reinterpret_cast<uintptr_t>(E_bf16) & 15) == 0,
@@ -627,7 +663,7 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     }
 
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
-                 int32_t*, float*, int);
+                 int32_t*, float*, int, const Presort);
 #define VQ_PICK3(NS, EW, P)                                                                       \
     (mode == 3 ? assign_tc_kernel<false, EW, 3, P> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P>  \
                                                  : mode == 1 ? assign_tc_kernel<NS, EW, 1, P> : assign_tc_kernel<NS, EW, 0, P>)
@@ -678,7 +714,7 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     if (verbose)
         fprintf(stderr, "vq_assign: N=%lld K=%d D=%d pair=%d mode=%d nstages=%d nabuf=%d norm_smem=%d grid=%u smem=%zu\n",
                 (long long)N, K, D, (int)pair, mode, nstages, nabuf, (int)norm_smem, cfg.gridDim.x, smem_total);
-    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg);
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg, ps);
     if (le != cudaSuccess && pair && attempt == 0) {  // cluster launch refused: fall back to the single-CTA kernel for good
         (void)cudaGetLastError();
         pair_unavailable = true;

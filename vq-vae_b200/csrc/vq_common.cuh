@@ -38,10 +38,19 @@ static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b;
 static inline int     round_up(int a, int b) { return (a + b - 1) / b * b; }
 
 // kernels implemented in the other translation units
+// VQ_SEARCH_PRESORT: the search kernels also leave, in the workspace, what the gather pass needs to visit rows in
+// code-sorted order -- per-code histogram, every row's rank inside its code, and (written by the block that finishes
+// last) the exclusive scan of the histogram.  All NULL = off.  hist / done must be zero when the kernel starts.
+struct Presort {
+    int* hist;    // [K]   rows per code
+    int* rank;    // [N]   rank of row n among the rows of its code (arrival order, not row order)
+    int* start;   // [K+1] exclusive scan of hist
+    int* done;    // [1]   blocks finished
+};
 int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const void* E_bf16, const float* e_norm2,
-                     int K, int32_t* idx, float* smin, cudaStream_t st);
+                     int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st);
 int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32,
-                       const float* e_norm2, int K, int32_t* idx, float* smin, cudaStream_t st);
+                       const float* e_norm2, int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st);
 int launch_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, cudaStream_t st);
 int launch_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, cudaStream_t st);
 size_t knn_workspace_bytes(int64_t N, int C);
@@ -54,7 +63,7 @@ void count_launch(int n = 1);
 
 // Byte offsets of the regions inside the caller-provided workspace.
 struct WsLayout {
-    size_t scal, zbf16, cnt, start, cursor, perm, partial, chunk_cnt, dpart, total;
+    size_t scal, zbf16, cnt, start, cursor, perm, rank, partial, chunk_cnt, dpart, total;
     int rows_per_chunk, nchunks;
 };
 WsLayout ws_layout(int64_t N, int K, int D, int in_dtype);
@@ -312,6 +321,9 @@ __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
+__device__ __forceinline__ void named_bar_arrive(int id, int nthreads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -331,6 +343,112 @@ __device__ __forceinline__ void st_stream_16(void* p, const int4& v) {
 }
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+// ---- VQ_SEARCH_PRESORT helpers (see struct Presort) -----------------------------------------
+// Warp-aggregated claim of one histogram slot per valid lane.  The atomic's result (`base`, meaningful on the
+// group's leader lane only) is NOT consumed here, so a caller can let it land while it does other work and finish
+// with presort_rank() later: rank = shfl(base, leader) + off.
+__device__ __forceinline__ void presort_claim(int* hist, int code, bool valid, int lane, int& base, int& leader,
+                                              int& off) {
+    const unsigned m = __match_any_sync(0xffffffffu, valid ? code : -1 - lane);
+    leader = __ffs(m) - 1;
+    off = __popc(m & ((1u << lane) - 1u));
+    base = 0;
+    if (valid && lane == leader) base = atomicAdd(hist + code, __popc(m));
+}
+__device__ __forceinline__ int presort_rank(int base, int leader, int off) {
+    return __shfl_sync(0xffffffffu, base, leader) + off;
+}
+// Called by EVERY thread of every block once the block's rows are claimed: the block that arrives last turns the
+// histogram into its exclusive scan start[0..K] and leaves the histogram ZERO again (so a caller that keeps the
+// workspace to itself never needs the memset: VQ_SEARCH_WS_CLEAN).  sh: >= 34 ints of shared memory.
+// K % 4 == 0: every thread owns 24 consecutive counters per round (six int4 loads issued together: one L2 round trip
+// and one block scan for K <= 24 * blockDim); otherwise a scalar walk over per-thread chunks.
+__device__ __forceinline__ void presort_finish(const Presort& P, int K, int* sh) {
+    // Every claim of this block has completed (its result was consumed for the rank store) and atomics are performed
+    // at L2; the barrier orders them before thread 0's acq_rel fence + counter increment (cumulative), so one fence per
+    // block is enough -- an all-thread __threadfence() (MEMBAR.SC) here costs microseconds per block.
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        const int last = atomicAdd(P.done, 1) == (int)gridDim.x - 1;
+        if (last) asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        sh[33] = last;
+    }
+    __syncthreads();
+    if (sh[33] == 0) return;
+    const int nt = blockDim.x, t = threadIdx.x, lane = t & 31, w = t >> 5, nw = (nt + 31) >> 5;
+    // exclusive prefix over the block of one value per thread (thread order); returns the prefix, *total = block sum
+    auto block_excl = [&](int v, int* total) {
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        __syncthreads();                         // sh[] of the previous round has been read
+        if (lane == 31) sh[w] = inc;
+        __syncthreads();
+        if (w == 0) {
+            const int x = lane < nw ? sh[lane] : 0;
+            int ix = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, ix, o);
+                if (lane >= o) ix += u;
+            }
+            sh[lane] = ix - x;
+            if (lane == 31) sh[32] = ix;
+        }
+        __syncthreads();
+        *total = sh[32];
+        return sh[w] + inc - v;
+    };
+    int carry = 0;
+    if ((K & 3) == 0) {
+        constexpr int T = 6;                     // tiles whose loads are in flight together
+        const int K4 = K >> 2;
+        const int4* h4 = reinterpret_cast<const int4*>(P.hist);
+        int4* s4 = reinterpret_cast<int4*>(P.start);
+        int4* z4 = reinterpret_cast<int4*>(P.hist);
+        for (int base = 0; base < K4; base += T * nt) {      // thread t owns T consecutive int4 (96 bytes) per round
+            const int i0 = base + t * T;
+            int4 v[T];
+            int s = 0;
+#pragma unroll
+            for (int j = 0; j < T; ++j) v[j] = i0 + j < K4 ? __ldcg(h4 + i0 + j) : make_int4(0, 0, 0, 0);
+#pragma unroll
+            for (int j = 0; j < T; ++j) s += v[j].x + v[j].y + v[j].z + v[j].w;
+            int tot;
+            int pre = carry + block_excl(s, &tot);
+#pragma unroll
+            for (int j = 0; j < T; ++j) {
+                if (i0 + j < K4) {
+                    s4[i0 + j] = make_int4(pre, pre + v[j].x, pre + v[j].x + v[j].y, pre + v[j].x + v[j].y + v[j].z);
+                    z4[i0 + j] = make_int4(0, 0, 0, 0);
+                }
+                pre += v[j].x + v[j].y + v[j].z + v[j].w;
+            }
+            carry += tot;
+        }
+    } else {
+        const int per = (K + nt - 1) / nt;
+        const int k0 = min(K, t * per), k1 = min(K, k0 + per);
+        int s = 0;
+        for (int k = k0; k < k1; ++k) s += __ldcg(P.hist + k);
+        int tot;
+        int run = block_excl(s, &tot);
+        for (int k = k0; k < k1; ++k) {
+            P.start[k] = run;
+            run += __ldcg(P.hist + k);
+            P.hist[k] = 0;
+        }
+        carry = tot;
+    }
+    if (t == 0) {
+        P.start[K] = carry;
+        *P.done = 0;
+    }
 }
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }

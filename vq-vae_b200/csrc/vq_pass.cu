@@ -139,6 +139,23 @@ scan_scatter_smem_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int 
     }
 }
 
+// VQ_STAT_PRESORTED: the search kernel already left the histogram's exclusive scan (`start`) and every row's rank
+// inside its code (vq_assign with VQ_SEARCH_PRESORT), so the counting sort is this one atomics-free scatter; like the
+// kernel above it clears the statistics buffers on the way.
+__global__ void __launch_bounds__(256)
+scatter_ranked_kernel(const int32_t* __restrict__ idx, const int* __restrict__ rank, int64_t N, int K,
+                      const int* __restrict__ start, int32_t* __restrict__ perm, float4* __restrict__ zero_a,
+                      int64_t na4, float* __restrict__ zero_b, int nb) {
+    const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, nth = (int64_t)gridDim.x * 256;
+    for (int64_t n = tid; n < N; n += nth) {
+        int c = idx[n];
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        perm[__ldg(start + c) + rank[n]] = (int32_t)n;
+    }
+    for (int64_t i = tid; i < na4; i += nth) zero_a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = tid; i < nb; i += nth) zero_b[i] = 0.f;
+}
+
 // one block; exclusive scan of cnt[0..K) -> start[0..K], cursor[k] = start[k].  Tiles of 4096 counters, int4 loads.
 __global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ cnt, int K, int* __restrict__ start,
                                                     int* __restrict__ cursor) {
@@ -653,17 +670,19 @@ WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
     size_t o = 0;
     L.scal = o;      o += 256;
     o += al((size_t)K * 4);                               // offset 256: rank-reduced counts of vq_ema_update_dp
-    L.zbf16 = o;     o += in_dtype == VQ_DT_F32 ? al((size_t)N * D * 2) : 0;
+    // the counter region sits at an offset that depends on K only (the VQ_SEARCH_WS_CLEAN contract is about it)
     L.cnt = o;       o += al((size_t)(2 * K + 4) * 4);     // [histogram K | cursor K | done counter]: one memset
     L.cursor = L.cnt + (size_t)K * 4;
     L.start = o;     o += al((size_t)(K + 1) * 4);
     L.perm = o;      o += al((size_t)N * 4);
+    L.rank = o;      o += al((size_t)N * 4);              // VQ_SEARCH_PRESORT: rank of every row inside its code
     L.partial = o;   o += al((size_t)(N + 64) * 4);       // generic kernel: one slot per row (+ discard slot)
     L.rows_per_chunk = (int)((ceil_div64(N, 256) + 31) / 32 * 32);
     if (L.rows_per_chunk < 1024) L.rows_per_chunk = 1024;
     L.nchunks = (int)ceil_div64(N, L.rows_per_chunk);
     L.chunk_cnt = o; o += al((size_t)L.nchunks * K * 4);
     L.dpart = o;     o += al((size_t)(ceil_div64(N, LG) + K + 1) * D * 4);   // deterministic mode: one slot per run
+    L.zbf16 = o;     o += in_dtype == VQ_DT_F32 ? al((size_t)N * D * 2) : 0;   // fp32 latents staged as bf16 for the search
     L.total = o;
     return L;
 }
@@ -696,8 +715,6 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     int32_t* perm = reinterpret_cast<int32_t*>(w + L.perm);
     float* part = reinterpret_cast<float*>(w + L.partial);
     int* chunk_cnt = reinterpret_cast<int*>(w + L.chunk_cnt);
-    // histogram, cursor and the pass kernel's completion counter are cleared by ONE memset
-    VQ_CHECK_CUDA(cudaMemsetAsync(cnt_i, 0, (size_t)(2 * K + 1) * 4, st));
     bool stats_cleared = false;
 
     const int es = in_dtype == VQ_DT_F32 ? 4 : 2;
@@ -705,6 +722,19 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     const bool vec_ok = D % epv == 0 && (ldz * es) % 16 == 0 && (ldq * es) % 16 == 0 &&
                         (reinterpret_cast<uintptr_t>(z) & 15) == 0 && (reinterpret_cast<uintptr_t>(q_out) & 15) == 0 &&
                         (reinterpret_cast<uintptr_t>(E_f32) & 15) == 0 && D / epv <= 128;
+    // VQ_STAT_PRESORTED: histogram, scan and ranks are already in ws (left by the search kernel); the pass kernel's
+    // completion counter is zero (the search's memset cleared it, and the pass resets it when it ends)
+    const bool presort_flag = (stat_kind & VQ_STAT_PRESORTED) != 0;
+    const bool presorted = presort_flag && vec_ok && stats && !deterministic;
+    stat_kind &= ~VQ_STAT_PRESORTED;
+    // a path that builds its own histogram in the counter region puts the zeros back afterwards when the caller works
+    // under the VQ_SEARCH_PRESORT / VQ_SEARCH_WS_CLEAN contract
+    struct Rezero {
+        int* p; size_t n; cudaStream_t st; bool on;
+        ~Rezero() { if (on) (void)cudaMemsetAsync(p, 0, n, st); }
+    } rezero{cnt_i, (size_t)(2 * K + 2) * 4, st, presort_flag && !presorted};
+    // otherwise histogram, cursor and the pass kernel's completion counter are cleared by ONE memset
+    if (!presorted) VQ_CHECK_CUDA(cudaMemsetAsync(cnt_i, 0, (size_t)(2 * K + 1) * 4, st));
     int64_t nparts = 0;
     if (!vec_ok) {
         const int64_t blocks = ceil_div64(N, 8);
@@ -737,6 +767,15 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                                                                            L.nchunks, perm);
                 count_launch(4);
                 dpart = reinterpret_cast<float*>(w + L.dpart);
+            } else if (presorted) {
+                const bool zero_here = !accum && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 && ((size_t)K * D) % 4 == 0;
+                const int64_t want = ceil_div64(N > (int64_t)K * D / 4 ? N : (int64_t)K * D / 4, 256 * 4);
+                const int gs = (int)(want < sm_count() * 8 ? (want < 1 ? 1 : want) : sm_count() * 8);
+                scatter_ranked_kernel<<<gs, 256, 0, st>>>(idx, reinterpret_cast<const int*>(w + L.rank), N, K, start, perm,
+                                                          reinterpret_cast<float4*>(code_sum),
+                                                          zero_here ? (int64_t)K * D / 4 : 0, code_cnt, zero_here ? K : 0);
+                count_launch(1);
+                stats_cleared = zero_here;
             } else if ((size_t)K * 12 <= 200 * 1024 && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 &&
                        ((size_t)K * D) % 4 == 0) {
                 // shared-memory privatised counting sort, 2 launches: block b owns R consecutive rows; the second

@@ -74,22 +74,30 @@ def prepare_codebook(E: torch.Tensor, search: str, E_bf16: Optional[torch.Tensor
 
 
 def assign(z: torch.Tensor, E: torch.Tensor, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor, search: str,
-           idx: torch.Tensor, smin: Optional[torch.Tensor], ws: Optional[torch.Tensor]) -> None:
+           idx: torch.Tensor, smin: Optional[torch.Tensor], ws: Optional[torch.Tensor], presort: bool = False,
+           ws_clean: bool = False) -> None:
+    """presort: the search also leaves the counting-sort inputs of idx (histogram, ranks, scan) in `ws`, so the
+    following gather_st_loss_scatter(..., presorted=True) on the same ws skips its histogram launches.
+    ws_clean: `ws` was zero-filled at allocation and has only ever been used by presort / presorted calls since."""
     _need_cuda(z, E, E_bf16, e_norm2, idx, smin, ws)
     N, D, ld = _rows(z)
     K = E.shape[0]
     assert idx.dtype == torch.int32 and idx.numel() >= N and idx.is_contiguous()
     assert smin is None or (smin.dtype == torch.float32 and smin.numel() >= N)
+    mode = SEARCH_MODES[search] | (_lib.VQ_SEARCH_PRESORT if presort else 0) | \
+        (_lib.VQ_SEARCH_WS_CLEAN if presort and ws_clean else 0)
     check(_lib.load().vq_assign(_ptr(z), _dt(z), N, D, ld, _ptr(E), _ptr(E_bf16), _ptr(e_norm2), K,
-                                SEARCH_MODES[search], _ptr(idx), _ptr(smin), _ptr(ws), _stream()), "vq_assign")
+                                mode, _ptr(idx), _ptr(smin), _ptr(ws), _stream()), "vq_assign")
 
 
 def gather_st_loss_scatter(z: torch.Tensor, idx: torch.Tensor, E: torch.Tensor, q_out: torch.Tensor,
                            sq_err_sum: torch.Tensor, code_cnt: Optional[torch.Tensor],
                            code_sum: Optional[torch.Tensor], stat_kind: int, deterministic: bool,
                            ws: Optional[torch.Tensor], accumulate: bool = False, idx64_out: Optional[torch.Tensor] = None,
-                           loss_out: Optional[torch.Tensor] = None, loss_scale: float = 0.0) -> None:
-    """accumulate: add to sq_err_sum / code_cnt / code_sum instead of overwriting (row chunks of one batch).
+                           loss_out: Optional[torch.Tensor] = None, loss_scale: float = 0.0,
+                           presorted: bool = False) -> None:
+    """presorted: idx was written by assign(..., presort=True) with the same z rows and ws (nothing touched since).
+    accumulate: add to sq_err_sum / code_cnt / code_sum instead of overwriting (row chunks of one batch).
     idx64_out [N] int64 / loss_out [1] fp32 (optional): the final indices widened to int64 and sq_err_sum * loss_scale,
     written by the pass itself (no torch elementwise kernels on the path)."""
     _need_cuda(z, idx, E, q_out, sq_err_sum, code_cnt, code_sum, ws, idx64_out, loss_out)
@@ -97,6 +105,8 @@ def gather_st_loss_scatter(z: torch.Tensor, idx: torch.Tensor, E: torch.Tensor, 
     assert loss_out is None or loss_out.dtype == torch.float32
     if accumulate:
         stat_kind |= _lib.VQ_STAT_ACCUMULATE
+    if presorted:
+        stat_kind |= _lib.VQ_STAT_PRESORTED
     N, D, ld = _rows(z)
     _, _, ldq = _rows(q_out)
     K = E.shape[0]

@@ -256,7 +256,9 @@ class VectorQuantizer(nn.Module):
         need = ops.workspace_bytes(N, self.codebook_size, self.emb_dim, dtype)
         dev = self.codebook.device
         if self._ws is None or self._ws.numel() < need or self._ws.device != dev:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            # zero-filled, and from here on used only by this module's presort / presorted calls: the counter region
+            # stays zero between steps (VQ_SEARCH_WS_CLEAN), so the search needs no memset in front of it
+            self._ws = torch.zeros(need, dtype=torch.uint8, device=dev)
         return self._ws
 
     def _use_peers(self) -> bool:
@@ -307,10 +309,12 @@ class VectorQuantizer(nn.Module):
         stats = self._stats_buffer()
         code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
         E = self.codebook.detach()
-        ops.assign(z2, E, self._E_bf16, self._e_norm2, search, idx32, None, ws)
+        # the search leaves the counting-sort inputs of idx in ws, the pass picks them up (one scatter launch instead of
+        # memset + histogram + scan/scatter)
+        ops.assign(z2, E, self._E_bf16, self._e_norm2, search, idx32, None, ws, presort=True, ws_clean=True)
         kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
         ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws,
-                                   idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N))
+                                   idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N), presorted=True)
         self._finish_step(code_cnt, code_sum, search, ws)
         return code_sum
 
@@ -490,10 +494,10 @@ class VectorQuantizer(nn.Module):
                 landed.append(ev)
         for c, (a, b) in enumerate(bounds):
             cur.wait_event(landed[c])
-            ops.assign(z_dev[a:b], E, self._E_bf16, self._e_norm2, search, idx32[a:b], None, ws)
+            ops.assign(z_dev[a:b], E, self._E_bf16, self._e_norm2, search, idx32[a:b], None, ws, presort=True, ws_clean=True)
             ops.gather_st_loss_scatter(z_dev[a:b], idx32[a:b], E, q[a:b], sqerr, code_cnt, code_sum, kind,
                                        self.deterministic, ws, accumulate=c > 0, idx64_out=idx64[a:b], loss_out=loss,
-                                       loss_scale=self._loss_scale(N))
+                                       loss_scale=self._loss_scale(N), presorted=True)
         if not bounds:
             ops.gather_st_loss_scatter(z_dev, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws,
                                        idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N))
