@@ -142,15 +142,38 @@ scan_scatter_smem_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int 
 // VQ_STAT_PRESORTED: the search kernel already left the histogram's exclusive scan (`start`) and every row's rank
 // inside its code (vq_assign with VQ_SEARCH_PRESORT), so the counting sort is this one atomics-free scatter; like the
 // kernel above it clears the statistics buffers on the way.
+// kVec: four consecutive rows per thread (idx and rank read as int4), one thread per group -- every load of the
+// idx -> start -> perm chain is in flight at once instead of a latency-bound loop (12.9 -> ~5 us at C2).
+template <bool kVec>
 __global__ void __launch_bounds__(256)
 scatter_ranked_kernel(const int32_t* __restrict__ idx, const int* __restrict__ rank, int64_t N, int K,
                       const int* __restrict__ start, int32_t* __restrict__ perm, float4* __restrict__ zero_a,
                       int64_t na4, float* __restrict__ zero_b, int nb) {
     const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, nth = (int64_t)gridDim.x * 256;
-    for (int64_t n = tid; n < N; n += nth) {
-        int c = idx[n];
-        if ((unsigned)c >= (unsigned)K) c = 0;
-        perm[__ldg(start + c) + rank[n]] = (int32_t)n;
+    if (kVec) {
+        const int64_t n4 = N >> 2;
+        for (int64_t g = tid; g < n4; g += nth) {
+            const int4 c = __ldcs(reinterpret_cast<const int4*>(idx) + g);
+            const int4 r = __ldcs(reinterpret_cast<const int4*>(rank) + g);
+            const int cc[4] = {c.x, c.y, c.z, c.w};
+            const int rr[4] = {r.x, r.y, r.z, r.w};
+            int st[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) st[j] = __ldg(start + ((unsigned)cc[j] < (unsigned)K ? cc[j] : 0));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) perm[st[j] + rr[j]] = (int32_t)(g * 4 + j);
+        }
+        for (int64_t n = (n4 << 2) + tid; n < N; n += nth) {
+            int c = idx[n];
+            if ((unsigned)c >= (unsigned)K) c = 0;
+            perm[__ldg(start + c) + rank[n]] = (int32_t)n;
+        }
+    } else {
+        for (int64_t n = tid; n < N; n += nth) {
+            int c = idx[n];
+            if ((unsigned)c >= (unsigned)K) c = 0;
+            perm[__ldg(start + c) + rank[n]] = (int32_t)n;
+        }
     }
     for (int64_t i = tid; i < na4; i += nth) zero_a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int64_t i = tid; i < nb; i += nth) zero_b[i] = 0.f;
@@ -326,8 +349,11 @@ __device__ __forceinline__ int4 lds_16(uint32_t addr) {
     return r;
 }
 
+#ifndef VQ_PASS_MINB
+#define VQ_PASS_MINB 1
+#endif
 template <typename T, int VPL, int LPR>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, VQ_PASS_MINB)
 pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __restrict__ idx,
             const int32_t* __restrict__ perm, const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
             float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
@@ -637,6 +663,8 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     static bool attr_set = false;              // one flag per template instance
     if (!attr_set) {
         cudaFuncSetAttribute(pass_kernel<T, VPL, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        // (left to the driver: forcing the largest shared-memory carve-out for a third block per SM shrinks L1, which
+        // the codebook-row and idx gathers live on -- C4 pass group 145 -> 160 us)
         attr_set = true;
     }
     pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, smem, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
@@ -769,11 +797,15 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                 dpart = reinterpret_cast<float*>(w + L.dpart);
             } else if (presorted) {
                 const bool zero_here = !accum && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 && ((size_t)K * D) % 4 == 0;
-                const int64_t want = ceil_div64(N > (int64_t)K * D / 4 ? N : (int64_t)K * D / 4, 256 * 4);
-                const int gs = (int)(want < sm_count() * 8 ? (want < 1 ? 1 : want) : sm_count() * 8);
-                scatter_ranked_kernel<<<gs, 256, 0, st>>>(idx, reinterpret_cast<const int*>(w + L.rank), N, K, start, perm,
-                                                          reinterpret_cast<float4*>(code_sum),
-                                                          zero_here ? (int64_t)K * D / 4 : 0, code_cnt, zero_here ? K : 0);
+                const bool vec4 = (reinterpret_cast<uintptr_t>(idx) & 15) == 0;
+                const int64_t work = vec4 ? ceil_div64(N, 4) : N;
+                const int64_t want = ceil_div64(work > (int64_t)K * D / 8 ? work : (int64_t)K * D / 8, 256);
+                const int gs = (int)(want < (int64_t)sm_count() * 32 ? (want < 1 ? 1 : want) : (int64_t)sm_count() * 32);
+                const int* rank = reinterpret_cast<const int*>(w + L.rank);
+                float4* za = reinterpret_cast<float4*>(code_sum);
+                const int64_t na4 = zero_here ? (int64_t)K * D / 4 : 0;
+                if (vec4) scatter_ranked_kernel<true><<<gs, 256, 0, st>>>(idx, rank, N, K, start, perm, za, na4, code_cnt, zero_here ? K : 0);
+                else scatter_ranked_kernel<false><<<gs, 256, 0, st>>>(idx, rank, N, K, start, perm, za, na4, code_cnt, zero_here ? K : 0);
                 count_launch(1);
                 stats_cleared = zero_here;
             } else if ((size_t)K * 12 <= 200 * 1024 && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 &&
