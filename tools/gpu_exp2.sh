@@ -1,7 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for w in c2 c4; do
-for p in 74 66 60 52; do
-for c in 4 8; do
-  VQ_ASSIGN_MAX_PAIRS=$p timeout 120 python tools/overlap_proto.py $w $c 2>&1 | tail -n 1 | tee -a gpurun_out/overlap.log
-done; done; done
+timeout 900 python -m pytest tests -q -m gpu -x --timeout=300 2>&1 | tail -n 3
+for v in "" _nobulk; do
+  echo "variant [$v]" | tee -a gpurun_out/exp2.log
+  VQ_B200_LIB=$PWD/vq-vae_b200/libvq_b200$v.so timeout 300 python tools/bench_kernels.py c2 c4 c1 c5 2>&1 | grep "stand-alone" | tee -a gpurun_out/exp2.log
+done

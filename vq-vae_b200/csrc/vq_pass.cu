@@ -327,6 +327,11 @@ template <> struct VecIO<float> {
 // thread copies exactly the 16-byte pieces it will later consume, so cp.async.wait_group is the only
 // synchronisation, no registers are tied up by loads in flight, and (STAGES - 1) * UB rows per lane group are
 // outstanding at any time -- memory-level parallelism independent of occupancy.
+#ifndef VQ_PASS_BULK
+#define VQ_PASS_BULK 0      // 0: per-lane cp.async ring (default); 1: one cp.async.bulk (TMA unit) per row + mbarriers --
+                            // measured slower (C4 pass group 146 -> 165 us, C1 46 -> 63 us): 256-512-byte bulk copies are
+                            // too small for the TMA unit, see profiles/r01/tuning_experiments.log
+#endif
 #ifndef VQ_PASS_STAGES
 #define VQ_PASS_STAGES 4
 #endif
@@ -369,12 +374,29 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     static_assert(LG % UB == 0 && NB >= S, "batching");
 
     extern __shared__ int4 pass_smem[];
+    const int lane = threadIdx.x & 31;
+    const int g = lane / LPR, lg = lane % LPR;
+#if VQ_PASS_BULK
+    // per lane group [S][UB] row slots of ROWB bytes (a latent row lands contiguously: one bulk copy per row), then
+    // [8 * G][S] mbarriers, then per warp [G][LG] row numbers and [G][LG] codes
+    constexpr int ROWB = VPL * LPR * 16;
+    const int grp = (threadIdx.x >> 5) * G + g;
+    const uint32_t ring_g = smem_u32(pass_smem) + (uint32_t)grp * (uint32_t)(S * UB * ROWB);
+    const uint32_t ring = ring_g + lg * 16u;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(pass_smem + S * UB * VPL * 256) + grp * S;
+    int* pos_base = reinterpret_cast<int*>(reinterpret_cast<uint64_t*>(pass_smem + S * UB * VPL * 256) + 8 * G * S) +
+                    (threadIdx.x >> 5) * (2 * G * LG);
+    if (lg == 0) {
+#pragma unroll
+        for (int i = 0; i < S; ++i) mbar_init(&bars[i], 1);
+        fence_mbar_init();
+    }
+    const uint32_t rowbytes = (uint32_t)D * (uint32_t)sizeof(T);
+#else
     // [S][UB][VPL][256] 16-byte ring slots, then per warp [G][LG] row numbers and [G][LG] codes
     const uint32_t ring = smem_u32(pass_smem) + threadIdx.x * 16u;
     int* pos_base = reinterpret_cast<int*>(pass_smem + S * UB * VPL * 256) + (threadIdx.x >> 5) * (2 * G * LG);
-
-    const int lane = threadIdx.x & 31;
-    const int g = lane / LPR, lg = lane % LPR;
+#endif
     const unsigned gmask = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << (g * LPR);
     const int64_t warp_global = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t p0 = (warp_global * G + g) * LG;
@@ -396,6 +418,30 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     }
     __syncwarp();
 
+#if VQ_PASS_BULK
+    // Latent rows reach shared memory as ONE bulk copy (TMA unit, cp.async.bulk) per row, issued by the group's first
+    // lane and completing on the stage's mbarrier: no per-lane cp.async instructions, and the bytes in flight are
+    // bounded by the ring, not by the L1 lines that LDGSTS requests occupy until their data returns.
+    auto issue = [&](int b) {                         // batch b of this lane group -> ring stage b % S
+        if (lg == 0) {
+            const int stage = b % S;
+            int nvalid = 0;
+#pragma unroll
+            for (int u = 0; u < UB; ++u) nvalid += prow[b * UB + u] >= 0;
+            mbar_arrive_expect_tx(&bars[stage], (uint32_t)nvalid * rowbytes);
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const int r = prow[b * UB + u];
+                if (r >= 0)
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 ::"r"(ring_g + (uint32_t)((stage * UB + u) * ROWB)), "l"(z + (int64_t)r * ldz),
+                                   "r"(rowbytes), "r"(smem_u32(&bars[stage])) : "memory");
+            }
+        }
+    };
+#pragma unroll
+    for (int b = 0; b < S - 1; ++b) issue(b);
+#else
     auto issue = [&](int b) {                         // batch b of this lane group -> ring stage b % S
         const int stage = b % S;
 #pragma unroll
@@ -414,6 +460,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
         issue(b);
         cp_async_commit();
     }
+#endif
 
     float e[VPL][EPV], acc[VPL][EPV];
     int4 qv[VPL];
@@ -461,10 +508,16 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
 
 #pragma unroll 1
     for (int b = 0; b < NB; ++b) {
+        const int stage = b % S;
+#if VQ_PASS_BULK
+        __syncwarp();                                 // every lane is done reading the stage the next copy overwrites
+        if (b + S - 1 < NB) issue(b + S - 1);
+        mbar_wait(&bars[stage], (uint32_t)(b / S) & 1u, 20);
+#else
         if (b + S - 1 < NB) issue(b + S - 1);
         cp_async_commit();                            // (possibly empty) group keeps the wait distance constant
         cp_async_wait<S - 1>();                       // batch b has landed in this thread's slots
-        const int stage = b % S;
+#endif
 #pragma unroll
         for (int u = 0; u < UB; ++u) {
             const int r = prow[b * UB + u];
@@ -476,7 +529,11 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
             for (int j = 0; j < VPL; ++j) {
                 const int v = lg + j * LPR;
                 zv[j] = make_int4(0, 0, 0, 0);
+#if VQ_PASS_BULK
+                if (valid && v < V) zv[j] = lds_16(ring + (uint32_t)((stage * UB + u) * ROWB + j * LPR * 16));
+#else
                 if (valid && v < V) zv[j] = lds_16(ring + (uint32_t)(((stage * UB + u) * VPL + j) * 256) * 16u);
+#endif
                 nf |= IO::nonfinite(zv[j]);
             }
             const bool bad = (__ballot_sync(0xffffffffu, valid && nf) & gmask) != 0;
@@ -659,7 +716,8 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     *nparts = blocks * 8;
     constexpr int U = PassCfg<VPL>::U;
     constexpr int UB = U < LPR ? U : LPR;
-    const size_t smem = (size_t)PASS_STAGES * UB * VPL * 256 * 16 + (size_t)8 * 2 * G * LG * sizeof(int);
+    const size_t smem = (size_t)PASS_STAGES * UB * VPL * 256 * 16 + (size_t)8 * 2 * G * LG * sizeof(int) +
+                        (VQ_PASS_BULK ? (size_t)8 * G * PASS_STAGES * 8 : 0);
     static bool attr_set = false;              // one flag per template instance
     if (!attr_set) {
         cudaFuncSetAttribute(pass_kernel<T, VPL, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
