@@ -1,7 +1,9 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -q -m gpu -x --timeout=300 2>&1 | tail -n 3
-for v in "" _nobulk; do
-  echo "variant [$v]" | tee -a gpurun_out/exp2.log
-  VQ_B200_LIB=$PWD/vq-vae_b200/libvq_b200$v.so timeout 300 python tools/bench_kernels.py c2 c4 c1 c5 2>&1 | grep "stand-alone" | tee -a gpurun_out/exp2.log
+for rep in 1 2; do
+for v in 0 31 30 1 6 24 14; do
+  for w in c4; do
+  VQ_PDL=$v timeout 300 python bench.py --skip-cpu --workload $w --steps 100 > gpurun_out/b.log 2>&1; echo "PDL=$v $w $(tail -n 1 gpurun_out/b.log | grep -o '"ms_per_step": [0-9.]*' | head -1)" | tee -a gpurun_out/exp2.log
+  done
+done
 done

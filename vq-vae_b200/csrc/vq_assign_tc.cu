@@ -232,6 +232,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     Ctl* ctl = reinterpret_cast<Ctl*>(smO + (kMode == 3 ? 4096 : 0));
     const uint8_t* aug_img = reinterpret_cast<const uint8_t*>(norms + num_nb * BN);   // behind the K_pad norms
 
+    pdl_wait();                   // the codebook shadow this kernel reads was written by the previous step's EMA kernel
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const uint32_t rank = kPair ? cluster_ctarank() : 0u;                 // 0 = leader (MMA issuer) of the pair
@@ -507,6 +508,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     }
 
 #ifndef VQ_PRESORT_NO_FINISH
+    pdl_trigger();                // this CTA's rows are done: the next kernel's launch may begin (it still waits for us)
     if (ps.hist != nullptr) presort_finish(ps, K, ctl->scan_sh);
 #endif
 
@@ -675,7 +677,7 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     VQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
 
     cudaLaunchConfig_t cfg = {};
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     cfg.blockDim = dim3(128 + 32 * epi_warps);
     cfg.dynamicSmemBytes = smem_total;
     cfg.stream = st;
@@ -714,6 +716,16 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     if (verbose)
         fprintf(stderr, "vq_assign: N=%lld K=%d D=%d pair=%d mode=%d nstages=%d nabuf=%d norm_smem=%d grid=%u smem=%zu\n",
                 (long long)N, K, D, (int)pair, mode, nstages, nabuf, (int)norm_smem, cfg.gridDim.x, smem_total);
+    {   // programmatic dependent launch: this grid may be set up while the previous kernel of the stream drains
+        int na = pair ? 1 : 0;
+        if (pdl_enabled(PDL_SEARCH)) {
+            attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
+        cfg.attrs = attr;
+        cfg.numAttrs = na;
+    }
     const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg, ps);
     if (le != cudaSuccess && pair && attempt == 0) {  // cluster launch refused: fall back to the single-CTA kernel for good
         (void)cudaGetLastError();

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/vq_b200.h"
 
@@ -317,6 +318,14 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- programmatic dependent launch ------------------------------------------------------
+// The kernels of one step form a chain on one stream.  Launched with the programmatic-stream-serialization attribute
+// (launch_pdl below), a kernel's grid may be set up while its predecessor is still draining; pdl_wait() -- the first
+// statement of every such kernel -- blocks until the predecessor has completed and its writes are visible, so only the
+// launch latency overlaps, never a data access.  pdl_trigger() lets the successor's launch begin.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- misc -------------------------------------------------------------------------------
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -457,5 +466,32 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+
+// host side of the above.  VQ_PDL in the environment is a bit mask over the kernels of the step (tuning knob):
+// 1 search, 2 scatter, 4 pass, 8 EMA totals, 16 EMA apply; 0 = plain stream order everywhere.
+enum { PDL_SEARCH = 1, PDL_SCATTER = 2, PDL_PASS = 4, PDL_TOTALS = 8, PDL_APPLY = 16, PDL_DEFAULT = 31 };
+inline bool pdl_enabled(int which) {
+    static int mask = -1;
+    if (mask < 0) {
+        const char* ev = getenv("VQ_PDL");
+        mask = ev == nullptr ? PDL_DEFAULT : atoi(ev);
+    }
+    return (mask & which) != 0;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(int which, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled(which) ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 }  // namespace vq
 #endif  // __CUDACC__

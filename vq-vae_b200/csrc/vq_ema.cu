@@ -68,6 +68,8 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
                   int32_t* __restrict__ steps_since_used, float* __restrict__ perplexity, int32_t* __restrict__ n_dead,
                   int dead_after, int update_usage, const Peers P, int64_t KD, float* __restrict__ cnt_red) {
     __shared__ double sh[3][32];
+    pdl_wait();
+    pdl_trigger();
     const int t = threadIdx.x;
     const float omg = 1.0f - decay;
     double s_n = 0.0, s_c = 0.0;
@@ -183,6 +185,8 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
                  const float* __restrict__ code_cnt, const float* __restrict__ code_sum, int K, int D, float decay,
                  float eps, float k_eps, int do_ema, int search, const Scal* __restrict__ scal,
                  __nv_bfloat16* __restrict__ E_bf16, float* __restrict__ e_norm2, int norm_elems, const Peers P) {
+    pdl_wait();
+    pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (k >= norm_elems) return;
@@ -306,13 +310,13 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                    "vq_ema_update: do_ema needs ema_cnt, ema_sum and code_sum");
         float* cnt_red = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256);    // reserved by ws_layout
         if (peer)
-            ema_totals_kernel<true><<<1, 1024, 0, st>>>(ema_cnt, code_cnt, K, decay, do_ema, scal, usage_total,
-                                                        steps_since_used, perplexity, n_dead, dead_after, update_usage,
-                                                        P, (int64_t)K * D, cnt_red);
+            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<true>, dim3(1), dim3(1024), 0, st, ema_cnt, code_cnt, K, decay, do_ema,
+                                     scal, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, P,
+                                     (int64_t)K * D, cnt_red));
         else
-            ema_totals_kernel<false><<<1, 1024, 0, st>>>(ema_cnt, code_cnt, K, decay, do_ema, scal, usage_total,
-                                                         steps_since_used, perplexity, n_dead, dead_after, update_usage,
-                                                         P, 0, nullptr);
+            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<false>, dim3(1), dim3(1024), 0, st, ema_cnt, code_cnt, K, decay,
+                                     do_ema, scal, usage_total, steps_since_used, perplexity, n_dead, dead_after,
+                                     update_usage, P, (int64_t)0, (float*)nullptr));
         if (peer) code_cnt = cnt_red;
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
@@ -321,14 +325,9 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
     }
     const int ne = round_up(K, 256);                 // codes incl. padding; vq_norm_elems(K) floats = ne norms + aug image
     const float k_eps = (float)((double)K * (double)eps);
-    if (peer && do_ema)
-        ema_apply_kernel<true><<<(ne + 7) / 8, 256, 0, st>>>(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps,
-                                                             k_eps, do_ema, search, scal,
-                                                             static_cast<__nv_bfloat16*>(E_bf16), e_norm2, ne, P);
-    else
-        ema_apply_kernel<false><<<(ne + 7) / 8, 256, 0, st>>>(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps,
-                                                              k_eps, do_ema, search, scal,
-                                                              static_cast<__nv_bfloat16*>(E_bf16), e_norm2, ne, P);
+    VQ_CHECK_CUDA(launch_pdl(PDL_APPLY, (peer && do_ema) ? ema_apply_kernel<true> : ema_apply_kernel<false>, dim3((ne + 7) / 8),
+                             dim3(256), 0, st, E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, k_eps, do_ema,
+                             search, static_cast<const Scal*>(scal), static_cast<__nv_bfloat16*>(E_bf16), e_norm2, ne, P));
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

@@ -149,6 +149,8 @@ __global__ void __launch_bounds__(256)
 scatter_ranked_kernel(const int32_t* __restrict__ idx, const int* __restrict__ rank, int64_t N, int K,
                       const int* __restrict__ start, int32_t* __restrict__ perm, float4* __restrict__ zero_a,
                       int64_t na4, float* __restrict__ zero_b, int nb) {
+    pdl_wait();
+    pdl_trigger();
     const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, nth = (int64_t)gridDim.x * 256;
     if (kVec) {
         const int64_t n4 = N >> 2;
@@ -364,6 +366,8 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
             float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
             float* __restrict__ dpart, int stat_kind, int* __restrict__ done, float* __restrict__ sq_err_out,
             const PassExtra X) {
+    pdl_wait();
+    pdl_trigger();
     using IO = VecIO<T>;
     constexpr int EPV = IO::EPV;
     constexpr int G = 32 / LPR;
@@ -725,9 +729,9 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
         // the codebook-row and idx gathers live on -- C4 pass group 145 -> 160 us)
         attr_set = true;
     }
-    pass_kernel<T, VPL, LPR><<<(unsigned)blocks, 256, smem, st>>>(static_cast<const T*>(z), N, D, ldz, idx, perm, E, K,
-                                                              static_cast<T*>(q), ldq, part, code_cnt, code_sum,
-                                                              dpart, stat_kind, done, sq_err, X);
+    VQ_CHECK_CUDA(launch_pdl(PDL_PASS, pass_kernel<T, VPL, LPR>, dim3((unsigned)blocks), dim3(256), smem, st, static_cast<const T*>(z),
+                             N, D, ldz, idx, perm, E, K, static_cast<T*>(q), ldq, part, code_cnt, code_sum, dpart, stat_kind,
+                             done, sq_err, X));
     return VQ_OK;
 }
 
@@ -862,8 +866,8 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                 const int* rank = reinterpret_cast<const int*>(w + L.rank);
                 float4* za = reinterpret_cast<float4*>(code_sum);
                 const int64_t na4 = zero_here ? (int64_t)K * D / 4 : 0;
-                if (vec4) scatter_ranked_kernel<true><<<gs, 256, 0, st>>>(idx, rank, N, K, start, perm, za, na4, code_cnt, zero_here ? K : 0);
-                else scatter_ranked_kernel<false><<<gs, 256, 0, st>>>(idx, rank, N, K, start, perm, za, na4, code_cnt, zero_here ? K : 0);
+                VQ_CHECK_CUDA(launch_pdl(PDL_SCATTER, vec4 ? scatter_ranked_kernel<true> : scatter_ranked_kernel<false>, dim3(gs), dim3(256),
+                                         0, st, idx, rank, N, K, start, perm, za, na4, code_cnt, zero_here ? K : 0));
                 count_launch(1);
                 stats_cleared = zero_here;
             } else if ((size_t)K * 12 <= 200 * 1024 && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 &&
