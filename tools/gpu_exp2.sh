@@ -1,9 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for rep in 1 2; do
-for v in 0 31 30 1 6 24 14; do
-  for w in c4; do
-  VQ_PDL=$v timeout 300 python bench.py --skip-cpu --workload $w --steps 100 > gpurun_out/b.log 2>&1; echo "PDL=$v $w $(tail -n 1 gpurun_out/b.log | grep -o '"ms_per_step": [0-9.]*' | head -1)" | tee -a gpurun_out/exp2.log
-  done
-done
-done
+timeout 900 python -m pytest tests -q -m gpu -x --timeout=300 2>&1 | tail -n 1
+for w in c2 c4; do for d in gaussian trained; do
+  timeout 300 python bench.py --skip-cpu --workload $w --data $d > gpurun_out/b.log 2>&1; echo "$w $d $(tail -n 1 gpurun_out/b.log | grep -o '"ms_per_step": [0-9.]*\|"ms_per_launch": [0-9.]*' | tr '\n' ' ')" | tee -a gpurun_out/exp2.log
+done; done
