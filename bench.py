@@ -222,7 +222,8 @@ def run_native(args, wl):
     split = None
     if n_type:
         from vqvae_b200 import SplitQuantizer
-        split = SplitQuantizer(D, D, K, channel_first=False, beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5).to(dev)
+        split = SplitQuantizer(D, D, K, channel_first=False, beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5,
+                               overlap=os.environ.get("VQ_SPLIT_OVERLAP", "") != "0").to(dev)
         split.quant_phase = mod
         with torch.no_grad():
             split.quant_type.codebook.copy_(E.flip(0)); split.quant_type.ema_sum.copy_(E.flip(0))
@@ -322,7 +323,7 @@ def run_native(args, wl):
                                   "ms_per_launch": t_assign}
         line_extra["roofline_pass"] = {"kernel": "scatter_ranked_kernel + pass_kernel (a-2..a-5; histogram / ranks / scan come from the search kernel)", "bound": "hbm",
                                        "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
-                                       "traffic": load_traffic(args.workload, "pass_kernel"),
+                                       "traffic": load_traffic(args.workload, "pass_group"),
                                        "algorithmic_bytes": pass_bytes, "peak_source": peaks["src"],
                                        "ms_per_launch": t_pass}
         line_extra["cpu_baseline"] = cpu_baseline(wl) if (world == 1 and not args.skip_cpu) else None

@@ -13,6 +13,10 @@
 //   warp 0      TMA producer (one elected lane; in a pair both CTAs load, completion goes to the leader's barriers)
 //   warp 1      tcgen05.mma issuer (one elected lane; in a pair the leader CTA only)
 //   warp 2      TMEM allocator / deallocator
+//   warp 3      VQ_SEARCH_PRESORT only: takes each slab's final indices from the epilogue (shared memory, named barriers)
+//               and claims their slots in the per-code histogram (warp-aggregated atomics) -> rank of every row inside
+//               its code; the block that finishes last scans the histogram (presort_finish).  The gather pass then
+//               needs no histogram launches of its own.
 //   warps 4..   epilogue (8 warps in pairs, 16 on single CTAs): warp w reads TMEM lanes 32*(w%4)..+31 (one row per
 //               thread) and one column part of each tile; the parts are merged through shared memory per slab.
 //

@@ -3,8 +3,9 @@
 //
 // HBM-bound: algorithmic traffic is D*s (read z) + 4 (idx) + D*s (write q) bytes per latent vector; the fp32
 // master codebook (K*D*4 <= 8 MiB at K=8192, D=256) stays L2-resident.  To keep the scatter-add off the L2
-// atomic units, rows are visited in CODE-SORTED order: a counting sort of idx (histogram -> exclusive scan ->
-// slot claim; 3 tiny kernels touching 4 bytes per row) yields `perm`, and every lane group then walks 64
+// atomic units, rows are visited in CODE-SORTED order: a counting sort of idx yields `perm` -- with VQ_STAT_PRESORTED
+// the histogram, its scan and every row's rank come out of the search kernel and one atomics-free scatter is left
+// here; stand-alone calls run histogram -> scan + slot claim themselves -- and every lane group then walks 64
 // consecutive sorted positions, keeping the running per-code sum in registers and issuing one vector `red`
 // per (code, 64-row slice) -- about K + N/64 reds of D floats per step instead of N.
 // Required by: scripts/export_codebook.py:104 (gather from [K, D]); frl/config/frl_model_v0.yaml:35 (straight
