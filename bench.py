@@ -223,7 +223,7 @@ def run_native(args, wl):
     if n_type:
         from vqvae_b200 import SplitQuantizer
         split = SplitQuantizer(D, D, K, channel_first=False, beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5,
-                               overlap=os.environ.get("VQ_SPLIT_OVERLAP", "") != "0").to(dev)
+                               overlap=os.environ.get("VQ_SPLIT_OVERLAP", "") == "1").to(dev)
         split.quant_phase = mod
         with torch.no_grad():
             split.quant_type.codebook.copy_(E.flip(0)); split.quant_type.ema_sum.copy_(E.flip(0))

@@ -161,6 +161,14 @@ int vq_knn_topk(const float* X, int64_t N, int C, const float* coords, const int
 int vq_knn_mutual_pairs(const int64_t* knn_idx, int64_t N, int k, int64_t* pairs, int64_t* n_pairs, void* ws,
                         vq_stream_t stream);
 
+/* Programmatic dependent launch along the step's kernel chain (search -> scatter -> pass -> EMA totals -> EMA apply):
+ * every kernel starts with griddepcontrol.wait and is launched with the stream-serialization attribute, so the next
+ * grid is set up while the current one drains.  mask bits: 1 search, 2 scatter, 4 pass, 8 EMA totals, 16 EMA apply
+ * (default 31, or VQ_PDL from the environment); returns the previous mask.  A caller that runs several chains
+ * concurrently on different streams should pass 0: early-resident grids of one chain can keep the other chain's
+ * CTA pairs off the SMs (measured: two-stream C3 step 0.89 -> 1.2 ms in one run out of three). */
+int vq_set_pdl_mask(int mask);
+
 /* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
 int64_t vq_launch_count(void);
 

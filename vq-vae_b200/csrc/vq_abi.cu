@@ -3,6 +3,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "vq_common.cuh"
@@ -19,6 +20,17 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+static std::atomic<int> g_pdl_mask{-1};
+int pdl_mask() {
+    int m = g_pdl_mask.load(std::memory_order_relaxed);
+    if (m < 0) {
+        const char* ev = getenv("VQ_PDL");
+        m = ev == nullptr ? 31 : (atoi(ev) & 31);
+        g_pdl_mask.store(m, std::memory_order_relaxed);
+    }
+    return m;
+}
 
 int sm_count() {
     static int cached_dev = -1, cached = 0;
@@ -52,6 +64,11 @@ extern "C" {
 int vq_abi_version(void) { return VQ_ABI_VERSION; }
 const char* vq_last_error(void) { return g_err; }
 int64_t vq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+int vq_set_pdl_mask(int mask) {
+    const int prev = pdl_mask();
+    g_pdl_mask.store(mask & 31, std::memory_order_relaxed);
+    return prev;
+}
 
 // K_pad fp32 norms followed by the K_pad x 32 B "aug" image (vq_ema.cu: write_aug)
 int vq_norm_elems(int K) { return K <= 0 ? 0 : round_up(K, 256) * 9; }

@@ -470,14 +470,8 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 // host side of the above.  VQ_PDL in the environment is a bit mask over the kernels of the step (tuning knob):
 // 1 search, 2 scatter, 4 pass, 8 EMA totals, 16 EMA apply; 0 = plain stream order everywhere.
 enum { PDL_SEARCH = 1, PDL_SCATTER = 2, PDL_PASS = 4, PDL_TOTALS = 8, PDL_APPLY = 16, PDL_DEFAULT = 31 };
-inline bool pdl_enabled(int which) {
-    static int mask = -1;
-    if (mask < 0) {
-        const char* ev = getenv("VQ_PDL");
-        mask = ev == nullptr ? PDL_DEFAULT : atoi(ev);
-    }
-    return (mask & which) != 0;
-}
+int pdl_mask();                                  // vq_abi.cu: VQ_PDL from the environment, or the last vq_set_pdl_mask()
+inline bool pdl_enabled(int which) { return (pdl_mask() & which) != 0; }
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(int which, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                               Args... args) {

@@ -60,6 +60,12 @@ def workspace_bytes(N: int, K: int, D: int, dtype: torch.dtype) -> int:
     return int(out.value)
 
 
+def set_pdl_mask(mask: int) -> int:
+    """Programmatic dependent launch along the step's kernel chain (include/vq_b200.h: vq_set_pdl_mask); returns the
+    previous mask.  0 = plain stream order (what concurrent chains on several streams should use)."""
+    return int(_lib.load().vq_set_pdl_mask(int(mask)))
+
+
 def launch_count() -> int:
     return int(_lib.load().vq_launch_count())
 

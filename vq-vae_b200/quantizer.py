@@ -528,15 +528,18 @@ class VectorQuantizer(nn.Module):
 class SplitQuantizer(nn.Module):
     """Two codebooks for the live model's two latent streams (BASELINE config 3): a `type` codebook over
     z_type [B, D_type, H, W] and a `phase` codebook over z_phase [B, D_phase, T, H, W] (attributes `quant_type`, `quant_phase`)
-    (frl/models/representation.py:60-72, :317-374; both channel-first).  The two quantisers share nothing, so the
-    type stream (T times fewer vectors) runs on a side CUDA stream underneath the phase stream's kernels.
+    (frl/models/representation.py:60-72, :317-374; both channel-first).  The two quantisers share nothing; they run back to
+    back on the caller's stream.  `overlap=True` puts the type stream (T times fewer vectors) on a side CUDA stream under
+    the phase stream's kernels: 5 % faster when it works, but two persistent one-CTA-per-SM searches compete for the same
+    SMs and one step in three to five ran 1.4-1.9x slower on B200 (profiles/r01/tuning_experiments.log), so it is off by
+    default (and switches programmatic dependent launch off while both chains are in flight).
 
     forward(z_type, z_phase) -> ((q_type, loss_type, idx_type), (q_phase, loss_phase, idx_phase)); `loss` is the sum
     the training step adds to its objective, `perplexity` a dict.
     """
 
     def __init__(self, type_dim: int, phase_dim: int, codebook_size: int, channel_first: bool = True,
-                 overlap: bool = True, **kw):
+                 overlap: bool = False, **kw):
         super().__init__()
         self.quant_type = VectorQuantizer(type_dim, codebook_size, channel_first=channel_first, **kw)
         self.quant_phase = VectorQuantizer(phase_dim, codebook_size, channel_first=channel_first, **kw)
@@ -568,9 +571,15 @@ class SplitQuantizer(nn.Module):
             if self._side is None or self._side.device != z_type.device:
                 self._side = torch.cuda.Stream(device=z_type.device)
             self._side.wait_stream(cur)                      # z_type was produced on the caller's stream
-            with torch.cuda.stream(self._side):
-                out_t = self.quant_type(z_type)
-            out_p = self.quant_phase(z_phase)
+            # two kernel chains in flight at once: no programmatic dependent launch (a chain's early-resident grids can
+            # keep the other chain's CTA pairs off the SMs: 0.89 -> 1.2 ms in one step out of three)
+            prev_mask = ops.set_pdl_mask(0)
+            try:
+                with torch.cuda.stream(self._side):
+                    out_t = self.quant_type(z_type)
+                out_p = self.quant_phase(z_phase)
+            finally:
+                ops.set_pdl_mask(prev_mask)
             cur.wait_stream(self._side)
             for t in out_t:                                  # allocated on the side stream, consumed on the caller's
                 t.record_stream(cur)
