@@ -1,0 +1,93 @@
+"""The counting-sort by-product of the search (VQ_SEARCH_PRESORT / VQ_STAT_PRESORTED / VQ_SEARCH_WS_CLEAN, include/vq_b200.h)
+and the launch-chain switch (vq_set_pdl_mask): the module keeps ONE zero-filled workspace and never clears it again, so
+every path through it -- tensor-core and fp32 search, vector / generic / deterministic pass, growing and shrinking
+batches, both latent dtypes -- must leave the counter region zero for the next step.  Checked end to end: a module
+stepping through a sequence of different batches must track the CPU oracle step by step."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import vq_reference as R
+
+pytestmark = pytest.mark.gpu
+
+
+def _lockstep(mod, ref, batches, tol, D):
+    for z in batches:
+        E_before = mod.codebook.detach().clone()
+        E_ref_before = ref.codebook.detach().clone()       # ema mode: the forward updates the codebook after the search
+        qr, lr, ir = ref(z)
+        qc, lc, ic = mod(z.cuda())
+        rep = R.near_tie_report(z.reshape(-1, D).float(), E_ref_before, ic.cpu().reshape(-1), ir.reshape(-1),
+                                precision=ref.precision)
+        assert rep["hard"] == 0, rep
+        assert torch.equal(qc.detach().reshape(-1, D), E_before[ic.reshape(-1)].to(z.dtype)), "gather must be bit-exact"
+        if rep["mismatch"] == 0:                     # a legitimate near-tie flip changes loss and statistics slightly
+            np.testing.assert_allclose(float(lc), float(lr), rtol=tol)
+            np.testing.assert_allclose(mod.codebook.detach().cpu().numpy(), ref.codebook.detach().numpy(), rtol=tol,
+                                       atol=1e-6)
+            assert torch.equal(mod.usage_total.cpu(), ref.usage_total)
+
+
+@pytest.mark.parametrize("search,dtype,D,deterministic", [
+    ("bf16", torch.bfloat16, 64, False),      # tensor-core search, vector pass: the production pairing
+    ("bf16", torch.float32, 64, False),       # fp32 latents staged as bf16 (staging region sits behind the counters)
+    ("fp32", torch.float32, 32, False),       # CUDA-core search leaves the same by-product
+    ("fp32", torch.float32, 20, False),       # D % 4 != 0 for the 16-byte path: generic pass ignores the by-product
+    ("bf16", torch.bfloat16, 64, True),       # deterministic pass builds its own stable sort, must re-zero the counters
+])
+def test_one_workspace_across_changing_batches(search, dtype, D, deterministic):
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(3)
+    K = 96
+    prec = "bf16" if search == "bf16" else "fp32"
+    ref = R.VectorQuantizerOracle(D, K, beta=0.25, quantizer="ema", ema_decay=0.9, precision=prec)
+    mod = VectorQuantizer(D, K, beta=0.25, quantizer="ema", ema_decay=0.9, search=search, deterministic=deterministic,
+                          cuda_graph=False)
+    mod.load_state_dict(ref.state_dict(), strict=False)
+    mod = mod.cuda()
+    g = torch.Generator().manual_seed(11)
+    sizes = [3000, 257, 40000, 1, 3000, 40000, 129]       # grows (new zero-filled workspace) and shrinks (same workspace)
+    batches = [torch.randn(n, D, generator=g).to(dtype) for n in sizes]
+    _lockstep(mod, ref, batches, 1e-3 if prec == "bf16" or dtype == torch.bfloat16 else 1e-5, D)
+
+
+def test_alternating_modes_share_the_workspace():
+    """deterministic on / off and eval / train flips on the same module: every combination must hand a clean counter region
+    to the next one."""
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(5)
+    K, D = 64, 32
+    ref = R.VectorQuantizerOracle(D, K, beta=0.25, quantizer="ema", ema_decay=0.95, precision="bf16")
+    mod = VectorQuantizer(D, K, beta=0.25, quantizer="ema", ema_decay=0.95, search="bf16", cuda_graph=False)
+    mod.load_state_dict(ref.state_dict(), strict=False)
+    mod = mod.cuda()
+    g = torch.Generator().manual_seed(2)
+    for step, (det, train) in enumerate([(False, True), (True, True), (False, False), (False, True), (True, False),
+                                         (False, True)]):
+        mod.deterministic = det
+        mod.train(train)
+        ref.train(train)
+        z = torch.randn(2048 + 64 * step, D, generator=g).to(torch.bfloat16)
+        _lockstep(mod, ref, [z], 1e-3, D)
+
+
+def test_pdl_mask_round_trip_and_results_do_not_depend_on_it():
+    from vqvae_b200 import VectorQuantizer, ops
+    prev = ops.set_pdl_mask(0)
+    try:
+        assert ops.set_pdl_mask(31) == 0 and ops.set_pdl_mask(5) == 31 and ops.set_pdl_mask(0) == 5
+        outs = []
+        for mask in (0, 31):
+            ops.set_pdl_mask(mask)
+            torch.manual_seed(9)
+            mod = VectorQuantizer(64, 128, quantizer="ema", search="bf16", deterministic=True, cuda_graph=False).cuda()
+            z = torch.randn(20000, 64, generator=torch.Generator().manual_seed(4)).to(torch.bfloat16).cuda()
+            for _ in range(3):
+                q, loss, idx = mod(z)
+            torch.cuda.synchronize()
+            outs.append((q.clone(), float(loss), idx.clone(), mod.codebook.detach().clone()))
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][2], outs[1][2])
+        assert outs[0][1] == outs[1][1] and torch.equal(outs[0][3], outs[1][3])
+    finally:
+        ops.set_pdl_mask(prev)
