@@ -32,6 +32,11 @@ int pdl_mask() {
     return m;
 }
 
+int current_device() {
+    int dev = -1;
+    return cudaGetDevice(&dev) == cudaSuccess ? dev : -1;
+}
+
 int sm_count() {
     static int cached_dev = -1, cached = 0;
     int dev = 0;

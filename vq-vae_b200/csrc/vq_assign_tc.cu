@@ -701,9 +701,12 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
         static int max_pairs = 0;
         static const void* cached_kern = nullptr;
         static size_t cached_smem = 0;
-        if (max_pairs == 0 || cached_kern != (const void*)kern || cached_smem != smem_total) {
+        static int cached_dev = -1;
+        const int cur_dev = current_device();
+        if (max_pairs == 0 || cached_kern != (const void*)kern || cached_smem != smem_total || cached_dev != cur_dev) {
             cached_kern = (const void*)kern;
             cached_smem = smem_total;
+            cached_dev = cur_dev;
             cfg.gridDim = dim3((unsigned)(sm_count() & ~1));
             int nc = 0;
             if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) != cudaSuccess || nc <= 0) {

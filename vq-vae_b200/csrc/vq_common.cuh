@@ -16,6 +16,7 @@ namespace vq {
 
 void set_error(const char* fmt, ...);          // thread-local message behind vq_last_error()
 int  sm_count();                               // cached cudaDevAttrMultiProcessorCount of the current device
+int  current_device();                         // cudaGetDevice, -1 on failure (function attributes are per device)
 
 #define VQ_CHECK_CUDA(expr)                                                              \
     do {                                                                                 \

@@ -507,12 +507,13 @@ int launch_knn_topk(const float* X, int64_t N, int C, const float* coords, const
     if (N == 0) return VQ_OK;
     VQ_REQUIRE(X != nullptr && knn_idx != nullptr && ws != nullptr, "vq_knn_topk: NULL argument");
     VQ_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "vq_knn_topk: ws must be 256-byte aligned");
-    static bool attr_set = false;
-    if (!attr_set) {
+    static int attr_dev = -1;                  // function attributes are per device
+    const int cur_dev = current_device();
+    if (attr_dev != cur_dev) {
         VQ_CHECK_CUDA(cudaFuncSetAttribute(knn_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         VQ_CHECK_CUDA(cudaFuncSetAttribute(knn_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         VQ_CHECK_CUDA(cudaFuncSetAttribute(knn_tile_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
+        attr_dev = cur_dev;
     }
     const KnnWs w = knn_ws_layout(N, C, sm_count());
     uint8_t* base = static_cast<uint8_t*>(ws);

@@ -366,7 +366,9 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
             const int32_t* __restrict__ perm, const float* __restrict__ E, int K, T* __restrict__ q, int64_t ldq,
             float* __restrict__ loss_partial, float* __restrict__ code_cnt, float* __restrict__ code_sum,
             float* __restrict__ dpart, int stat_kind, int* __restrict__ done, float* __restrict__ sq_err_out,
-            const PassExtra X) {
+            const PassExtra X, const int lgr) {
+    // lgr <= LG: sorted positions per lane group (64 for large batches; 16 / 32 when N is small, so that a 40 960-row
+    // batch still spreads over every SM: 160 blocks instead of 40)
     pdl_wait();
     pdl_trigger();
     using IO = VecIO<T>;
@@ -374,9 +376,9 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     constexpr int G = 32 / LPR;
     constexpr int U = PassCfg<VPL>::U;
     constexpr int UB = U < LPR ? U : LPR;             // rows per batch
-    constexpr int NB = LG / UB;                       // batches per lane group
     constexpr int S = PASS_STAGES;
-    static_assert(LG % UB == 0 && NB >= S, "batching");
+    static_assert(LG % UB == 0 && 16 % UB == 0 && 16 / UB >= S - 1, "batching");
+    const int NB = lgr / UB;                          // batches per lane group
 
     extern __shared__ int4 pass_smem[];
     const int lane = threadIdx.x & 31;
@@ -404,7 +406,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
 #endif
     const unsigned gmask = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << (g * LPR);
     const int64_t warp_global = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int64_t p0 = (warp_global * G + g) * LG;
+    const int64_t p0 = (warp_global * G + g) * lgr;
     const int V = D / EPV;
     int* prow = pos_base + g * LG;
     int* pcode = pos_base + (G + g) * LG;
@@ -413,7 +415,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
     for (int i = 0; i < LG / LPR; ++i) {
         const int64_t pos = p0 + i * LPR + lg;
         int r = -1, c = -1;
-        if (pos < N) {
+        if (i * LPR + lg < lgr && pos < N) {
             r = perm != nullptr ? perm[pos] : (int)pos;
             c = idx[r];
             if ((unsigned)c >= (unsigned)K) c = 0;
@@ -715,7 +717,13 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
                   int K, void* q, int64_t ldq, float* part, int64_t* nparts, float* code_cnt, float* code_sum,
                   float* dpart, int stat_kind, int* done, float* sq_err, PassExtra X, cudaStream_t st) {
     constexpr int G = 32 / LPR;
-    const int64_t groups = ceil_div64(N, LG);
+    // rows per lane group: 64, fewer while that leaves SMs without a block (deterministic mode sizes its slots for 64)
+    int lgr = LG;
+    if (dpart == nullptr) {
+        const int64_t want_groups = (int64_t)sm_count() * 2 * 8 * G;          // two blocks per SM
+        while (lgr > 16 && ceil_div64(N, lgr) < want_groups) lgr >>= 1;
+    }
+    const int64_t groups = ceil_div64(N, lgr);
     const int64_t warps = ceil_div64(groups, G);
     const int64_t blocks = ceil_div64(warps, 8);
     *nparts = blocks * 8;
@@ -723,16 +731,17 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     constexpr int UB = U < LPR ? U : LPR;
     const size_t smem = (size_t)PASS_STAGES * UB * VPL * 256 * 16 + (size_t)8 * 2 * G * LG * sizeof(int) +
                         (VQ_PASS_BULK ? (size_t)8 * G * PASS_STAGES * 8 : 0);
-    static bool attr_set = false;              // one flag per template instance
-    if (!attr_set) {
+    static int attr_dev = -1;                  // per template instance; function attributes are per device
+    const int cur_dev = current_device();
+    if (attr_dev != cur_dev) {
         cudaFuncSetAttribute(pass_kernel<T, VPL, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         // (left to the driver: forcing the largest shared-memory carve-out for a third block per SM shrinks L1, which
         // the codebook-row and idx gathers live on -- C4 pass group 145 -> 160 us)
-        attr_set = true;
+        attr_dev = cur_dev;
     }
     VQ_CHECK_CUDA(launch_pdl(PDL_PASS, pass_kernel<T, VPL, LPR>, dim3((unsigned)blocks), dim3(256), smem, st, static_cast<const T*>(z),
                              N, D, ldz, idx, perm, E, K, static_cast<T*>(q), ldq, part, code_cnt, code_sum, dpart, stat_kind,
-                             done, sq_err, X));
+                             done, sq_err, X, lgr));
     return VQ_OK;
 }
 
@@ -878,11 +887,12 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                 int R = (int)ceil_div64(N, 2 * sm_count());
                 R = round_up(R < 1024 ? 1024 : R, 1024);
                 const int nb = (int)ceil_div64(N, R);
-                static bool attr_set = false;
-                if (!attr_set) {
+                static int attr_dev = -1;      // function attributes are per device
+                const int cur_dev = current_device();
+                if (attr_dev != cur_dev) {
                     VQ_CHECK_CUDA(cudaFuncSetAttribute(hist_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
                     VQ_CHECK_CUDA(cudaFuncSetAttribute(scan_scatter_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-                    attr_set = true;
+                    attr_dev = cur_dev;
                 }
                 hist_smem_kernel<<<nb, 512, (size_t)K * 4, st>>>(idx, N, K, R, cnt_i);
                 scan_scatter_smem_kernel<<<nb, 512, (size_t)K * 12, st>>>(idx, N, K, R, cnt_i, cursor, perm,
