@@ -178,6 +178,7 @@ class VectorQuantizer(nn.Module):
         self.manager: Optional[CodebookManager] = None
         # scratch (never in the state dict)
         self._E_bf16 = self._e_norm2 = self._ws = self._stats = None
+        self._ws_need = {}
         self._shadow_key = None
         self.cuda_graph = bool(cuda_graph)
         self._graphs: dict = {}
@@ -253,7 +254,11 @@ class VectorQuantizer(nn.Module):
         self._shadow_key = key
 
     def _workspace(self, N: int, dtype: torch.dtype) -> torch.Tensor:
-        need = ops.workspace_bytes(N, self.codebook_size, self.emb_dim, dtype)
+        need = self._ws_need.get((N, dtype))
+        if need is None:                              # one ctypes call per new (rows, dtype), not per step
+            if len(self._ws_need) > 64:
+                self._ws_need.clear()
+            need = self._ws_need[(N, dtype)] = ops.workspace_bytes(N, self.codebook_size, self.emb_dim, dtype)
         dev = self.codebook.device
         if self._ws is None or self._ws.numel() < need or self._ws.device != dev:
             # zero-filled, and from here on used only by this module's presort / presorted calls: the counter region
