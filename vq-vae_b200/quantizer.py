@@ -19,6 +19,8 @@ forward() on a CPU tensor raises: the kernels are sm_100a only and there is no f
 """
 from __future__ import annotations
 
+import contextlib
+
 import os
 from typing import Optional
 
@@ -69,6 +71,9 @@ def extract_code_usage_from_state(state: dict, prefix: str = "") -> torch.Tensor
         if k.startswith(prefix) and k.endswith("usage_total"):
             return v.detach().cpu().to(torch.int64)
     raise KeyError("no '*usage_total' entry in the state dict")
+
+
+_NULL_CTX = contextlib.nullcontext()
 
 
 class _VQFunction(torch.autograd.Function):
@@ -360,11 +365,16 @@ class VectorQuantizer(nn.Module):
                     else:
                         self._graphs[key] = ent
                 if ent is not None:
-                    g, sz, sq_, si32, si64, ssq, sloss, code_sum, n_launch = ent
+                    g, sz, sout, nq, code_sum, n_launch, _scratch = ent
                     sz.copy_(z2)
                     g.replay()
                     self.graph_launches += n_launch
-                    return sq_.clone(), sloss.clone(), si64.clone(), code_sum
+                    # q, indices and loss live in ONE static byte buffer: one clone (one copy kernel, one allocation)
+                    # hands all three to the caller -- autograd keeps q, so the outputs cannot alias the static buffer
+                    out = sout.clone()
+                    return (out[:N * D * z2.element_size()].view(z2.dtype).view(N, D),
+                            out[nq + 8 * N:nq + 8 * N + 4].view(torch.float32),
+                            out[nq:nq + 8 * N].view(torch.int64), code_sum)
         q = torch.empty((N, D), dtype=z2.dtype, device=dev)
         idx32 = torch.empty(N, dtype=torch.int32, device=dev)
         idx64 = torch.empty(N, dtype=torch.int64, device=dev)
@@ -377,11 +387,13 @@ class VectorQuantizer(nn.Module):
         N, D = z2.shape
         dev = z2.device
         sz = torch.empty((N, D), dtype=z2.dtype, device=dev)
-        sq_ = torch.empty((N, D), dtype=z2.dtype, device=dev)
+        nq = (N * D * z2.element_size() + 15) // 16 * 16       # [q | pad | idx int64 | loss fp32 | pad] in one buffer
+        sout = torch.empty(nq + 8 * N + 16, dtype=torch.uint8, device=dev)
+        sq_ = sout[:N * D * z2.element_size()].view(z2.dtype).view(N, D)
+        si64 = sout[nq:nq + 8 * N].view(torch.int64)
+        sloss = sout[nq + 8 * N:nq + 8 * N + 4].view(torch.float32)
         si32 = torch.empty(N, dtype=torch.int32, device=dev)
-        si64 = torch.empty(N, dtype=torch.int64, device=dev)
         ssq = torch.empty(1, dtype=torch.float32, device=dev)
-        sloss = torch.empty(1, dtype=torch.float32, device=dev)
         self._workspace(N, z2.dtype)                 # sized before capture: the graph holds its address
         self._stats_buffer()
         g = torch.cuda.CUDAGraph()
@@ -392,7 +404,8 @@ class VectorQuantizer(nn.Module):
         # tensors, a DataLoader's pin-memory thread) must not invalidate it
         with torch.cuda.graph(g, capture_error_mode="relaxed"):
             code_sum = self._step_kernels(sz, sq_, si32, si64, ssq, sloss, search)
-        return (g, sz, sq_, si32, si64, ssq, sloss, code_sum, ops.launch_count() - l0)
+        # (si32, ssq): scratch the captured launches write; it must live as long as the graph does
+        return (g, sz, sout, nq, code_sum, ops.launch_count() - l0, (si32, ssq))
 
     # ------------------------------------------------------------------ a-6 .. a-9
     def _finish_step(self, code_cnt, code_sum, search: str, ws) -> None:
@@ -426,7 +439,9 @@ class VectorQuantizer(nn.Module):
             return self._forward_channel_first(z)
         if z.shape[-1] != self.emb_dim:
             raise ValueError(f"last dimension {z.shape[-1]} != emb_dim {self.emb_dim}")
-        with torch.autocast(device_type="cuda", enabled=False):
+        # the autocast guard and the autograd node cost ~30 us of host time per call, which is what bounds a small-batch
+        # step (C1 replays in ~55 us of GPU time): enter them only when they have something to do
+        with (torch.autocast(device_type="cuda", enabled=False) if torch.is_autocast_enabled("cuda") else _NULL_CTX):
             lead = z.shape[:-1]
             in_dtype = z.dtype
             z2 = z.reshape(-1, self.emb_dim)
@@ -437,7 +452,12 @@ class VectorQuantizer(nn.Module):
                 z2 = z2.to(torch.float32)
             if z2.shape[0] > 1 and (z2.stride(1) != 1 or z2.stride(0) < self.emb_dim):
                 z2 = z2.contiguous()
-            q, loss, idx = _VQFunction.apply(z2, self.codebook, self, search)
+            if torch.is_grad_enabled() and (z2.requires_grad or self.codebook.requires_grad):
+                q, loss, idx = _VQFunction.apply(z2, self.codebook, self, search)
+            else:
+                self._ensure_shadow(search)
+                q, loss, idx, _ = self._run_step(z2, search)
+                loss = loss.reshape(())
             if q.dtype != in_dtype:
                 q = q.to(in_dtype)
             return q.reshape(*lead, self.emb_dim), loss, idx.reshape(lead)
