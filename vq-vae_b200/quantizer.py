@@ -489,6 +489,13 @@ class VectorQuantizer(nn.Module):
         if not zh.is_pinned():
             zh = zh.pin_memory()
         N = zh.shape[0]
+        if chunks is None and N > 0 and self._graph_wanted(zh):
+            # a small batch is one chunk: nothing to hide the copy under, so it goes in front of the graph-replayed step
+            self._ensure_shadow(search)
+            q, loss, idx64, _ = self._run_step(zh.to(dev, non_blocking=True), search)
+            if q.dtype != z_host.dtype:
+                q = q.to(z_host.dtype)
+            return q.reshape(*lead, D), loss.reshape(()), idx64.reshape(lead)
         if chunks is None:                      # ~128 K rows per chunk: transfer time per chunk well above launch costs
             chunks = max(1, min(16, N // 131072))
         rows = max(128, -(-N // max(1, chunks)) // 128 * 128) if N > 0 else 1
