@@ -1,8 +1,8 @@
 #!/bin/bash
-# experiment trip: parity tests, kernel timings, short bench lines
+# experiment trip: parity tests, then A/B of a library variant (VQ_B200_LIB) on gaussian and trained-like latents
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -q -m gpu -x --timeout=300 2>&1 | tail -n 2
-timeout 300 python tools/bench_kernels.py c2 c4 c1 2>&1 | grep "stand-alone" | tee gpurun_out/kern.log
-for w in c1 c2 c4; do
-  timeout 300 python bench.py --skip-cpu --workload $w --steps 100 > gpurun_out/bench_$w.log 2>&1; echo "$w $(tail -n 1 gpurun_out/bench_$w.log | grep -o '"ms_per_step": [0-9.]*' | tr '\n' ' ')"
-done
+for rep in 1 2; do for v in "" _noblk; do for w in c2 c4; do for d in gaussian trained; do
+  VQ_B200_LIB=$PWD/vq-vae_b200/libvq_b200$v.so timeout 300 python bench.py --skip-cpu --workload $w --data $d > gpurun_out/b.log 2>&1
+  echo "lib[$v] $w $d $(tail -n 1 gpurun_out/b.log | grep -o '"ms_per_step": [0-9.]*\|"ms_per_launch": [0-9.]*' | tr '\n' ' ')" | tee -a gpurun_out/ab.log
+done; done; done; done

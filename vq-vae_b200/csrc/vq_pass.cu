@@ -338,6 +338,9 @@ template <> struct VecIO<float> {
                             // measured slower (C4 pass group 146 -> 165 us, C1 46 -> 63 us): 256-512-byte bulk copies are
                             // too small for the TMA unit, see profiles/r01/tuning_experiments.log
 #endif
+#ifndef VQ_PASS_BLOCKSUM
+#define VQ_PASS_BLOCKSUM 1   // 1: lane groups whose last run is the block's first code leave as ONE red burst per block
+#endif
 #ifndef VQ_PASS_STAGES
 #define VQ_PASS_STAGES 4
 #endif
@@ -427,6 +430,19 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
         pcode[i * LPR + lg] = c;
     }
     __syncwarp();
+#if VQ_PASS_BLOCKSUM
+    // A code with many rows (trained codebooks: a fifth of all rows can share one code) spans whole blocks, and every
+    // lane group of such a block would fire its own red burst at the same 4*D bytes of code_sum (C2, Zipf-like usage:
+    // pass group 198 us against 163 us on uniform usage).  Lane groups whose LAST run is the code the block starts with
+    // hand their sums over through shared memory (the ring, idle by then) and leave as one burst per block.
+    __shared__ int blk_code;
+    __shared__ int blk_cnts[8 * G];
+    const bool blk_on = code_sum != nullptr && dpart == nullptr && perm != nullptr;     // block-uniform
+    if (blk_on) {
+        if (threadIdx.x == 0) blk_code = pcode[0];    // warp 0, lane group 0, position 0: the block's first sorted row
+        __syncthreads();
+    }
+#endif
 
 #if VQ_PASS_BULK
     // Latent rows reach shared memory as ONE bulk copy (TMA unit, cp.async.bulk) per row, issued by the group's first
@@ -603,7 +619,51 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
             }
         }
     }
+#if VQ_PASS_BLOCKSUM
+    {
+        const bool mine = blk_on && cur >= 0 && cur == blk_code && cnt > 0;
+        if (!mine) flush();
+        if (blk_on) {
+            constexpr int ROWF = VPL * LPR * EPV;     // floats per lane-group slot
+            const int grp_i = (threadIdx.x >> 5) * G + g;
+            float* slots = reinterpret_cast<float*>(pass_smem);
+            __syncthreads();                          // every lane group is done with the ring
+            if (lg == 0) blk_cnts[grp_i] = mine ? cnt : 0;
+            if (mine) {
+#pragma unroll
+                for (int j = 0; j < VPL; ++j) {
+                    const int v = lg + j * LPR;
+                    if (v < V) {
+#pragma unroll
+                        for (int x = 0; x < EPV; x += 4)
+                            *reinterpret_cast<float4*>(slots + grp_i * ROWF + v * EPV + x) =
+                                make_float4(acc[j][x], acc[j][x + 1], acc[j][x + 2], acc[j][x + 3]);
+                    }
+                }
+            }
+            __syncthreads();
+            int total = 0;
+#pragma unroll
+            for (int i = 0; i < 8 * G; ++i) total += blk_cnts[i];
+            if (total > 0) {
+                float* dst = code_sum + (int64_t)blk_code * D;
+                for (int i = threadIdx.x * 4; i < D; i += 256 * 4) {
+                    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int gi = 0; gi < 8 * G; ++gi) {          // fixed order
+                        if (blk_cnts[gi] > 0) {
+                            const float4 t = *reinterpret_cast<const float4*>(slots + gi * ROWF + i);
+                            sum.x += t.x; sum.y += t.y; sum.z += t.z; sum.w += t.w;
+                        }
+                    }
+                    red_add_v4(dst + i, sum.x, sum.y, sum.z, sum.w);
+                }
+                if (threadIdx.x == 0) atomicAdd(code_cnt + blk_code, (float)total);
+            }
+        }
+    }
+#else
     flush();
+#endif
     loss = warp_sum(loss);
     if (lane == 0) loss_partial[warp_global] = loss;
 
