@@ -18,7 +18,7 @@
  * stream has drained) unless it says "host".  Every function enqueues work on `stream` and returns without
  * synchronising.  Return value 0 = ok; otherwise one of VQ_ERR_* and vq_last_error() holds a message
  * (thread-local).  No torch / ATen types appear here; the Python side binds these with ctypes
- * (vq-vae_b200/_lib.py) -- see INTEGRATION.md.  There is no CPU fallback behind any of these.
+ * (vqvae_b200/_lib.py) -- see INTEGRATION.md.  There is no CPU fallback behind any of these.
  */
 #ifndef VQ_B200_H_
 #define VQ_B200_H_

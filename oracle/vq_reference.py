@@ -19,7 +19,7 @@ contract the reference scripts impose:
   * straight_through: true -> frl/config/frl_model_v0.yaml:35
 
 Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline / ``--impl
-reference`` legs may import this module.  The product (``vq-vae_b200``) never does.
+reference`` legs may import this module.  The product (``vqvae_b200``) never does.
 
 Choices that no reference line pins are marked (CHOICE) below and listed in DESIGN.md.
 """
@@ -213,7 +213,7 @@ class StepStats:
 
 
 class VectorQuantizerOracle(nn.Module):
-    """Same object contract as ``vq-vae_b200`` 's VectorQuantizer, pure torch, CPU.
+    """Same object contract as ``vqvae_b200`` 's VectorQuantizer, pure torch, CPU.
 
     forward(z [..., D]) -> (quantized [..., D] same dtype, loss fp32 scalar, indices int64 [...]).
     Order inside one training forward (CHOICE): search with the *current* codebook, emit

@@ -1,7 +1,10 @@
-"""Import alias for the ``vq-vae_b200/`` package (a hyphen cannot appear in a Python module name)."""
-import os as _os
+"""vqvae_b200: the FoR-EST vector-quantisation hot path on B200 (sm_100a) kernels.
 
-_real = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "vq-vae_b200")
-__path__ = [_real]
-with open(_os.path.join(_real, "__init__.py")) as _fh:
-    exec(compile(_fh.read(), _os.path.join(_real, "__init__.py"), "exec"))
+Only what the hot path needs lives in this package: ``csrc/`` (CUDA + C ABI), ``_lib`` (ctypes binding),
+``ops`` (tensor -> pointer wrappers), ``quantizer`` (the nn.Module the reference scripts call), ``parallel``
+(data-parallel statistics exchange) and ``knn`` (the mutual-kNN pair mining of the live training step).
+(``vq-vae_b200`` at the repo root is a symlink to this directory: a hyphen cannot appear in a module name.)
+"""
+from .quantizer import CodebookManager, SplitQuantizer, VectorQuantizer, extract_code_usage_from_state  # noqa: F401
+
+__all__ = ["VectorQuantizer", "SplitQuantizer", "CodebookManager", "extract_code_usage_from_state"]

@@ -72,8 +72,8 @@ def load(build_if_missing: bool = False) -> C.CDLL:
             _build.build()
         else:
             raise VQLibError(
-                f"{LIB_PATH} is missing: build it with `python vq-vae_b200/build.py` (nvcc, sm_100a). "
-                "The vq-vae_b200 ops have no fallback path.")
+                f"{LIB_PATH} is missing: build it with `python vqvae_b200/build.py` (nvcc, sm_100a). "
+                "The vqvae_b200 ops have no fallback path.")
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)          # AttributeError here = header/library mismatch

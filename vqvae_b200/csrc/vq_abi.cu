@@ -25,8 +25,12 @@ static std::atomic<int> g_pdl_mask{-1};
 int pdl_mask() {
     int m = g_pdl_mask.load(std::memory_order_relaxed);
     if (m < 0) {
-        const char* ev = getenv("VQ_PDL");
+#ifdef VQ_TUNING
+        const char* ev = getenv("VQ_PDL");           // tuning build only; the product takes vq_set_pdl_mask()
         m = ev == nullptr ? 31 : (atoi(ev) & 31);
+#else
+        m = 31;
+#endif
         g_pdl_mask.store(m, std::memory_order_relaxed);
     }
     return m;

@@ -86,10 +86,12 @@ template <bool kNormSmem, int kMode>
 __device__ __forceinline__ void fold_chunk(const uint32_t (&r)[32], const float* __restrict__ nrm_g, uint32_t nrm_s,
                                            int col0, float& best, int& bidx, uint32_t slot, uint32_t slot_stride, int dbg = 0) {
     float s[32];
-    if (dbg == 3) {
+#ifdef VQ_TUNING
+    if (dbg == 3) {                    // timing experiment (results are WRONG): no norm loads, no FFMA
 #pragma unroll
         for (int j = 0; j < 32; ++j) s[j] = __uint_as_float(r[j]);
     } else
+#endif
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         float4 n4;
@@ -221,8 +223,14 @@ template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair>
 __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
                  const __grid_constant__ CUtensorMap tm_aug, const float* __restrict__ norms, int64_t N, int K, int D,
-                 int nkb, int nstages, int nabuf, int32_t* __restrict__ idx, float* __restrict__ smin, int dbg,
+                 int nkb, int nstages, int nabuf, int32_t* __restrict__ idx, float* __restrict__ smin,
+#ifdef VQ_TUNING
+                 int dbg,               // 1..4: timing experiments of the tuning build (results are WRONG); 0 = off
+#endif
                  const Presort ps) {
+#ifndef VQ_TUNING
+    constexpr int dbg = 0;             // the product build has no result-changing switches
+#endif
     constexpr int B_ROWS = kPair ? BN / 2 : BN;          // codes of a stage held by this CTA
     constexpr int B_ST = B_ROWS * BK * 2;                // ring slot bytes (16 KiB / 32 KiB)
     extern __shared__ uint8_t smem_raw[];
@@ -605,17 +613,24 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
                "vq_assign(bf16): z and E_bf16 must be 16-byte aligned");
     const int nkb = (D + BK - 1) / BK;
     const int num_nb = (K + BN - 1) / BN;
-    static int env_epi = -1, dbg = 0, mode_override = -1, pair_override = -1;
-    if (env_epi < 0) {
-        const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // tuning knob: 4, 8 or 16 epilogue warps
-        env_epi = (ev != nullptr && (atoi(ev) == 16 || atoi(ev) == 8 || atoi(ev) == 4)) ? atoi(ev) : 0;
-        ev = getenv("VQ_ASSIGN_DBG");                            // 1/2/3: timing experiments, results are WRONG
+    // The product build reads nothing from the environment: epilogue warps, epilogue mode and pairing follow the shape.
+    // Only the tuning build (build.py --variant, -DVQ_TUNING) has the knobs below, including timing experiments whose
+    // results are WRONG.
+    int env_epi = 0, mode_override = -1, pair_override = -1;
+#ifdef VQ_TUNING
+    static int t_epi = -1, dbg = 0, t_mode = -1, t_pair = -1;
+    if (t_epi < 0) {
+        const char* ev = getenv("VQ_ASSIGN_EPI_WARPS");          // 4, 8 or 16 epilogue warps
+        t_epi = (ev != nullptr && (atoi(ev) == 16 || atoi(ev) == 8 || atoi(ev) == 4)) ? atoi(ev) : 0;
+        ev = getenv("VQ_ASSIGN_DBG");                            // 1..4: timing experiments, results are WRONG
         if (ev != nullptr) dbg = atoi(ev);
         ev = getenv("VQ_ASSIGN_MODE");                           // force an epilogue mode (0..3)
-        if (ev != nullptr) mode_override = atoi(ev);
+        if (ev != nullptr) t_mode = atoi(ev);
         ev = getenv("VQ_ASSIGN_PAIR");                           // 0: single-CTA kernel, 1: CTA-pair kernel
-        if (ev != nullptr) pair_override = atoi(ev);
+        if (ev != nullptr) t_pair = atoi(ev);
     }
+    env_epi = t_epi; mode_override = t_mode; pair_override = t_pair;
+#endif
     // CTA pairs (cta_group::2) whenever there is more than one 128-row slab: a pair retires 256 rows in the time one CTA
     // retires 128, so the load balance over the SMs is the same and each SM pulls half the codebook bytes.
     static bool pair_unavailable = false;            // set once if this device / context cannot co-schedule CTA pairs
@@ -672,14 +687,24 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
         tm_aug = tm_e;                                 // never dereferenced
     }
 
+#ifdef VQ_TUNING
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
                  int32_t*, float*, int, const Presort);
+#else
+    void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
+                 int32_t*, float*, const Presort);
+#endif
 #define VQ_PICK3(NS, EW, P)                                                                       \
     (mode == 3 ? assign_tc_kernel<false, EW, 3, P> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P>  \
                                                  : mode == 1 ? assign_tc_kernel<NS, EW, 1, P> : assign_tc_kernel<NS, EW, 0, P>)
 #define VQ_PICK(NS, EW) (pair ? VQ_PICK3(NS, EW, true) : VQ_PICK3(NS, EW, false))
+#ifdef VQ_TUNING
     if (norm_smem) kern = epi_warps == 4 ? VQ_PICK(true, 4) : epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
     else kern = epi_warps == 4 ? VQ_PICK(false, 4) : epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
+#else       // product build: pairs run 8 epilogue warps, single CTAs 16 (14 instantiations instead of 42)
+    if (norm_smem) kern = pair ? VQ_PICK3(true, 8, true) : VQ_PICK3(true, 16, false);
+    else kern = pair ? VQ_PICK3(false, 8, true) : VQ_PICK3(false, 16, false);
+#endif
 #undef VQ_PICK
 #undef VQ_PICK3
     VQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
@@ -723,7 +748,11 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
         const int64_t ntiles = (N + BM - 1) / BM;
         cfg.gridDim = dim3((unsigned)(ntiles < sm_count() ? ntiles : sm_count()));
     }
+#ifdef VQ_TUNING
     static const bool verbose = getenv("VQ_ASSIGN_VERBOSE") != nullptr;
+#else
+    constexpr bool verbose = false;
+#endif
     if (verbose)
         fprintf(stderr, "vq_assign: N=%lld K=%d D=%d pair=%d mode=%d nstages=%d nabuf=%d norm_smem=%d grid=%u smem=%zu\n",
                 (long long)N, K, D, (int)pair, mode, nstages, nabuf, (int)norm_smem, cfg.gridDim.x, smem_total);
@@ -737,7 +766,11 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
         cfg.attrs = attr;
         cfg.numAttrs = na;
     }
+#ifdef VQ_TUNING
     const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg, ps);
+#else
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, ps);
+#endif
     if (le != cudaSuccess && pair && attempt == 0) {  // cluster launch refused: fall back to the single-CTA kernel for good
         (void)cudaGetLastError();
         pair_unavailable = true;

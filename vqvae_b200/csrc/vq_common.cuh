@@ -468,7 +468,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 }
 
 
-// host side of the above.  VQ_PDL in the environment is a bit mask over the kernels of the step (tuning knob):
+// host side of the above.  The mask (vq_set_pdl_mask; VQ_PDL in the environment of the tuning build) is a bit mask over the kernels of the step (tuning knob):
 // 1 search, 2 scatter, 4 pass, 8 EMA totals, 16 EMA apply; 0 = plain stream order everywhere.
 enum { PDL_SEARCH = 1, PDL_SCATTER = 2, PDL_PASS = 4, PDL_TOTALS = 8, PDL_APPLY = 16, PDL_DEFAULT = 31 };
 int pdl_mask();                                  // vq_abi.cu: VQ_PDL from the environment, or the last vq_set_pdl_mask()

@@ -785,12 +785,14 @@ int launch_pass_t(const void* z, int64_t N, int D, int64_t ldz, int32_t* idx, co
     if (dpart == nullptr) {
         const int64_t want_groups = (int64_t)sm_count() * 2 * 8 * G;          // two blocks per SM
         while (lgr > 16 && ceil_div64(N, lgr) < want_groups) lgr >>= 1;
+#ifdef VQ_TUNING
         static int env_lgr = -1;                 // tuning knob: VQ_PASS_LGR=<rows per lane group, multiple of 4, 16..64>
         if (env_lgr < 0) {
             const char* ev = getenv("VQ_PASS_LGR");
             env_lgr = ev != nullptr ? atoi(ev) : 0;
         }
         if (env_lgr >= 16 && env_lgr <= LG && env_lgr % 4 == 0) lgr = env_lgr;
+#endif
     }
     const int64_t groups = ceil_div64(N, lgr);
     const int64_t warps = ceil_div64(groups, G);

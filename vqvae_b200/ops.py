@@ -22,13 +22,13 @@ def _dt(t: torch.Tensor) -> int:
         return VQ_DT_BF16
     if t.dtype == torch.float32:
         return VQ_DT_F32
-    raise TypeError(f"vq-vae_b200 kernels take bfloat16 or float32 latents, got {t.dtype}")
+    raise TypeError(f"vqvae_b200 kernels take bfloat16 or float32 latents, got {t.dtype}")
 
 
 def _need_cuda(*ts: Optional[torch.Tensor]) -> None:
     for t in ts:
         if t is not None and not t.is_cuda:
-            raise RuntimeError("vq-vae_b200: this op runs only on CUDA tensors (sm_100a kernels, no CPU fallback); "
+            raise RuntimeError("vqvae_b200: this op runs only on CUDA tensors (sm_100a kernels, no CPU fallback); "
                                "use oracle/vq_reference.py for CPU checks")
 
 
