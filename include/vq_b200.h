@@ -125,6 +125,11 @@ int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D,
                      float* perplexity /* [1] */, int32_t* n_dead /* [1] */, int dead_after, int update_usage, void* ws,
                      const void* const* peer_stats /* host [world] */, void* const* peer_flags /* host [world] */,
                      int world, int rank, int epoch, vq_stream_t stream);
+/* Bound of the cross-rank wait inside vq_ema_update_dp, in milliseconds of wall-clock time (default 1 800 000 = 30 min;
+ * <= 0 waits for ever); returns the previous value.  It is a rendezvous of processes -- a rank may be late by seconds or
+ * minutes (rank-0-only validation, checkpointing, a data-loader stall) -- so it is NOT the kernels' internal hang bound.
+ * When it expires the waiting kernel traps and the launch fails with a CUDA error, like a collective's watchdog. */
+int64_t vq_set_peer_timeout_ms(int64_t ms);
 /* CUDA IPC plumbing for the above: cudaMalloc + zero + export a 64-byte handle / open a peer's handle / release. */
 int vq_ipc_alloc(size_t bytes, void** dev_ptr /* host out */, void* handle_out /* host, 64 bytes */);
 int vq_ipc_free(void* dev_ptr);

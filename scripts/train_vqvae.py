@@ -112,8 +112,9 @@ def train(args) -> dict:
               f"quantizer={args.quantizer} K={args.codebook_size} D={args.emb_dim}")
     net = model
     if world > 1:
-        if args.quantizer == "st":                       # same initial codebook on every rank
-            torch.distributed.broadcast(model.quant.codebook.data, src=0)
+        # every rank seeds its own RNG (seed + rank), DDP broadcasts parameters only (broadcast_buffers=False: the EMA
+        # state is the kernels' job) -- so the quantiser state, buffers included, is taken from rank 0 explicitly
+        model.quant.sync_state_from(0)
         net = nn.parallel.DistributedDataParallel(model, device_ids=[local], broadcast_buffers=False)
     codebook_params = [p for n, p in model.named_parameters() if ".quant.codebook" in n or n.endswith("quant.codebook")]
     other_params = [p for n, p in model.named_parameters()
@@ -143,12 +144,11 @@ def train(args) -> dict:
             if step == 0 and args.data_init:              # data-dependent codebook init from the first latents
                 with torch.no_grad(), torch.autocast(device_type="cuda", dtype=torch.bfloat16, enabled=amp and args.bf16):
                     model.quant.init_codebook_from(model.encode(batch["cont"]).float())
-                if world > 1:
-                    torch.distributed.broadcast(model.quant.codebook.data, src=0)
-                    model.quant.ema_sum.copy_(model.quant.codebook.data)
-            if args.reseed_every > 0 and step > 0 and step % args.reseed_every == 0 and world == 1:
-                with torch.no_grad():
+                model.quant.sync_state_from(0)
+            if args.reseed_every > 0 and step > 0 and step % args.reseed_every == 0:
+                with torch.no_grad():                     # DP: the dead set is identical on all ranks, rank 0's rows win
                     model.quant.reseed_dead_codes(model.encode(batch["cont"]).float())
+                model.quant.sync_state_from(0)
             for g in opt.param_groups:
                 g["lr"] = lr_at(step)
             opt.zero_grad(set_to_none=True)
@@ -174,6 +174,9 @@ def train(args) -> dict:
             scaler.update()
             step += 1
             count += 1
+            if step == 1 and world > 1:                   # replicas must be bit-identical from the first update on
+                from vqvae_b200 import parallel as _par
+                _par.assert_replicas_identical(model.quant.codebook)
             vec_seen += batch["cont"][..., 0].numel()
             if step % args.log_every == 0 or step == total_steps:       # host syncs only on logging steps
                 vals = {"recon_cont": float(loss_cont.detach()), "recon_cat": float(loss_cat.detach()), "canopy": float(loss_canopy.detach()),

@@ -31,6 +31,7 @@ SIGNATURES = {
     "vq_last_error": (C.c_char_p, []),
     "vq_launch_count": (_i64, []),
     "vq_set_pdl_mask": (_i, [_i]),
+    "vq_set_peer_timeout_ms": (_i64, [_i64]),
     "vq_norm_elems": (_i, [_i]),
     "vq_workspace_bytes": (_i, [_i64, _i, _i, _i, C.POINTER(C.c_size_t)]),
     "vq_prepare_codebook": (_i, [_p, _i, _i, _i, _p, _p, _p]),

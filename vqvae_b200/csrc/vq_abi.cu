@@ -36,6 +36,11 @@ int pdl_mask() {
     return m;
 }
 
+// Cross-rank rendezvous bound of the fused peer exchange: 30 minutes unless the host says otherwise (a torch process
+// group's own default is 10 minutes for NCCL; VectorQuantizer passes the group's timeout through vq_set_peer_timeout_ms).
+static std::atomic<long long> g_peer_timeout_ns{1800ll * 1000000000ll};
+long long peer_timeout_ns() { return g_peer_timeout_ns.load(std::memory_order_relaxed); }
+
 int current_device() {
     int dev = -1;
     return cudaGetDevice(&dev) == cudaSuccess ? dev : -1;
@@ -77,6 +82,11 @@ int vq_set_pdl_mask(int mask) {
     const int prev = pdl_mask();
     g_pdl_mask.store(mask & 31, std::memory_order_relaxed);
     return prev;
+}
+
+int64_t vq_set_peer_timeout_ms(int64_t ms) {
+    const long long prev = g_peer_timeout_ns.exchange(ms <= 0 ? 0 : (long long)ms * 1000000ll, std::memory_order_relaxed);
+    return prev / 1000000ll;
 }
 
 // K_pad fp32 norms followed by the K_pad x 32 B "aug" image (vq_ema.cu: write_aug)

@@ -62,6 +62,7 @@ int launch_knn_mutual(const int64_t* knn_idx, int64_t N, int k, int64_t* pairs, 
                       cudaStream_t st);
 bool assign_tc_supported(int64_t N, int D, int64_t ldz, int K);
 void count_launch(int n = 1);
+long long peer_timeout_ns();                   // bound of the cross-rank waits (vq_set_peer_timeout_ms), <= 0 = none
 
 // Byte offsets of the regions inside the caller-provided workspace.
 struct WsLayout {

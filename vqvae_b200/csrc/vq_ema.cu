@@ -25,7 +25,13 @@ struct Peers {
     const float* stats[VQ_MAX_PEERS];   // rank r's statistics buffer of this step (own buffer included)
     int32_t* flags[VQ_MAX_PEERS];       // rank r's flag array [VQ_MAX_PEERS]; slot s = last epoch signalled by rank s
     int world, rank, epoch;
+    long long timeout_ns;               // cross-rank wait bound (vq_set_peer_timeout_ms); <= 0: wait for ever
 };
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ float ld_peer(const float* p) {
     float v;
     asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
@@ -40,22 +46,42 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
     return v;
 }
 // Tell every rank that this rank's statistics of `epoch` are complete (they were written by earlier kernels of this
-// stream), then wait until every rank has said the same.  Bounded spin: a missing rank traps instead of hanging.
-__device__ __forceinline__ void peers_signal_and_wait(const Peers& P) {
+// stream), then wait until every rank has said the same.  The wait is a rendezvous of PROCESSES, not a protocol step
+// inside one kernel: a rank may arrive seconds or minutes late (rank-0-only validation or checkpointing, a data-loader
+// stall), so its bound is its own -- wall-clock (globaltimer), minutes by default, set by the host with
+// vq_set_peer_timeout_ms to match the process group's timeout -- and unrelated to the mbarrier hang bound.  The poll
+// backs off to one system-scope load per ~2 us so that a long wait does not hammer NVLink.  A rank that is still
+// missing when the bound expires traps (the launch fails with a CUDA error, like a collective's watchdog would).
+__device__ __forceinline__ void peers_wait(const Peers& P) {
     const int t = threadIdx.x;
     if (t < P.world) {
-        __threadfence_system();
-        st_release_sys(P.flags[t] + P.rank, P.epoch);
         const int32_t* mine = P.flags[P.rank] + t;
-        const long long t0 = clock64();
-        while (ld_acquire_sys(mine) < P.epoch) {
-            if (clock64() - t0 > VQ_HANG_CYCLES) {
-                printf("vq_b200: rank %d timed out waiting for rank %d (epoch %d)\n", P.rank, t, P.epoch);
-                __trap();
+        if (ld_acquire_sys(mine) < P.epoch) {
+            const unsigned long long t0 = globaltimer_ns();
+            unsigned ns = 32;
+            while (ld_acquire_sys(mine) < P.epoch) {
+                __nanosleep(ns);
+                if (ns < 2048) ns <<= 1;
+                if (P.timeout_ns > 0 && globaltimer_ns() - t0 > (unsigned long long)P.timeout_ns) {
+                    printf("vq_b200: rank %d waited %lld ms for rank %d (epoch %d): giving up\n", P.rank,
+                           P.timeout_ns / 1000000ll, t, P.epoch);
+                    __trap();
+                }
             }
         }
     }
     __syncthreads();
+}
+__device__ __forceinline__ void peers_signal(const Peers& P) {      // threads 0 .. world-1
+    const int t = threadIdx.x;
+    if (t < P.world) {
+        __threadfence_system();
+        st_release_sys(P.flags[t] + P.rank, P.epoch);
+    }
+}
+__device__ __forceinline__ void peers_signal_and_wait(const Peers& P) {
+    peers_signal(P);
+    peers_wait(P);
 }
 
 // one block.  tot_new = sum_k (g n_k + (1-g) cnt_k) in a fixed order (double); usage / dead / perplexity.
@@ -285,7 +311,7 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                       int dead_after, int update_usage, void* ws, cudaStream_t st, const void* const* peer_stats,
                       void* const* peer_flags, int world, int rank, int epoch) {
     Peers P;
-    P.world = 0; P.rank = 0; P.epoch = 0;
+    P.world = 0; P.rank = 0; P.epoch = 0; P.timeout_ns = peer_timeout_ns();
     const bool peer = peer_stats != nullptr;
     if (peer) {
         VQ_REQUIRE(world >= 1 && world <= VQ_MAX_PEERS && rank >= 0 && rank < world && peer_flags != nullptr && epoch > 0,

@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 from ._lib import check
-from .ops import _need_cuda, _ptr, _stream
+from .ops import _On, _ptr
 
 
 def _workspace(N: int, Cdim: int, device) -> torch.Tensor:
@@ -26,28 +26,28 @@ def _workspace(N: int, Cdim: int, device) -> torch.Tensor:
 def knn_topk(features: torch.Tensor, k: int, coords: Optional[torch.Tensor] = None,
              patch: Optional[torch.Tensor] = None, pos_min_spatial: float = 4.0, return_d2: bool = False):
     """[N, C] fp32 -> knn_idx [N, k] int64 (-1 = no valid neighbour) (+ squared distances)."""
-    _need_cuda(features, coords, patch)
-    X = features.detach().to(torch.float32).contiguous()
-    N, Cdim = X.shape
-    knn = torch.empty((N, k), dtype=torch.int64, device=X.device)
-    d2 = torch.empty((N, k), dtype=torch.float32, device=X.device) if return_d2 else None
-    ws = _workspace(N, Cdim, X.device)
-    if coords is not None:
-        coords = coords.detach().to(torch.float32).contiguous()
-        patch = patch.to(torch.int32).contiguous()
-    check(_lib.load().vq_knn_topk(_ptr(X), N, Cdim, _ptr(coords), _ptr(patch), float(pos_min_spatial), int(k), _ptr(knn),
-                                  _ptr(d2), _ptr(ws), _stream()), "vq_knn_topk")
+    with _On(features, coords, patch) as on:
+        X = features.detach().to(torch.float32).contiguous()
+        N, Cdim = X.shape
+        knn = torch.empty((N, k), dtype=torch.int64, device=X.device)
+        d2 = torch.empty((N, k), dtype=torch.float32, device=X.device) if return_d2 else None
+        ws = _workspace(N, Cdim, X.device)
+        if coords is not None:
+            coords = coords.detach().to(torch.float32).contiguous()
+            patch = patch.to(torch.int32).contiguous()
+        check(_lib.load().vq_knn_topk(_ptr(X), N, Cdim, _ptr(coords), _ptr(patch), float(pos_min_spatial), int(k),
+                                      _ptr(knn), _ptr(d2), _ptr(ws), on.stream), "vq_knn_topk")
     return (knn, d2) if return_d2 else knn
 
 
 def mutual_pairs(knn: torch.Tensor) -> torch.Tensor:
-    _need_cuda(knn)
-    N, k = knn.shape
-    pairs = torch.empty((max(N * k, 1), 2), dtype=torch.int64, device=knn.device)
-    n = torch.zeros(1, dtype=torch.int64, device=knn.device)
-    ws = _workspace(N, 4, knn.device)
-    check(_lib.load().vq_knn_mutual_pairs(_ptr(knn), N, k, _ptr(pairs), _ptr(n), _ptr(ws), _stream()),
-          "vq_knn_mutual_pairs")
+    with _On(knn) as on:
+        N, k = knn.shape
+        pairs = torch.empty((max(N * k, 1), 2), dtype=torch.int64, device=knn.device)
+        n = torch.zeros(1, dtype=torch.int64, device=knn.device)
+        ws = _workspace(N, 4, knn.device)
+        check(_lib.load().vq_knn_mutual_pairs(_ptr(knn), N, k, _ptr(pairs), _ptr(n), _ptr(ws), on.stream),
+              "vq_knn_mutual_pairs")
     return pairs[:int(n)]                     # the size is data dependent: one device -> host read, as in the reference
 
 

@@ -66,10 +66,15 @@ class PeerExchange:
     writes step t+1 (the flag exchange of step t+1 orders everything older).
     """
 
-    def __init__(self, numel: int, device: torch.device, group=None):
+    def __init__(self, numel: int, device: torch.device, group=None, timeout_s: Optional[float] = None):
         import ctypes as C
         from . import _lib
         lib = _lib.load()
+        # the cross-rank wait inside the kernels is a rendezvous of processes: bound it like a collective (minutes), not
+        # like a kernel-internal barrier.  VQ_PEER_TIMEOUT_S / timeout_s; default 30 min; 0 = wait for ever.
+        if timeout_s is None:
+            timeout_s = float(os.environ.get("VQ_PEER_TIMEOUT_S", "1800"))
+        lib.vq_set_peer_timeout_ms(int(timeout_s * 1000))
         self.group, self.numel, self.device = group, int(numel), device
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         if self.world > _lib.MAX_PEERS:

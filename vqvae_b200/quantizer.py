@@ -142,6 +142,8 @@ class VectorQuantizer(nn.Module):
     peer_exchange: "auto" (default) uses the fused peer-memory exchange (parallel.PeerExchange + vq_ema_update_dp)
         for the EMA statistics when the process group runs NCCL on one node, "nccl" always all-reduces with
         torch.distributed, "peer" insists on the fused path.
+    peer_timeout_s: wall-clock bound of the cross-rank wait on the fused path (default: VQ_PEER_TIMEOUT_S or 1800 s --
+        a rank may be minutes late because of rank-0-only validation or checkpointing; 0 waits for ever).
     process_group / sync_stats: with torch.distributed initialised, per-code counts and sums are
         all-reduced (SUM) before the EMA step so every rank applies the identical update.
     """
@@ -150,8 +152,9 @@ class VectorQuantizer(nn.Module):
                  ema_decay: float = 0.99, ema_eps: float = 1e-5, search: str = "auto",
                  dead_after: int = DEFAULT_DEAD_AFTER, deterministic: bool = False, process_group=None,
                  sync_stats: bool = True, channel_first: bool = False, peer_exchange: str = "auto",
-                 cuda_graph: bool = True):
+                 cuda_graph: bool = True, peer_timeout_s: Optional[float] = None):
         super().__init__()
+        self.peer_timeout_s = peer_timeout_s
         if quantizer not in ("st", "ema"):
             raise ValueError(f"quantizer must be 'st' or 'ema', got {quantizer!r}")
         if search not in ("auto", "bf16", "fp32"):
@@ -236,12 +239,33 @@ class VectorQuantizer(nn.Module):
         self._shadow_key = None
         return n
 
+    @torch.no_grad()
+    def sync_state_from(self, src: int = 0) -> None:
+        """Data-parallel runs: make every replica start from rank `src`'s quantiser state (codebook, EMA accumulators,
+        usage counters).  The buffers are initialised from the per-rank RNG, DistributedDataParallel is normally run with
+        broadcast_buffers=False around this module (the EMA update is the kernels' job, not DDP's), and identical
+        all-reduced updates applied to DIFFERENT states never converge to identical replicas -- so call this once after
+        construction / data-dependent init / re-seeding, on every rank."""
+        if not parallel.dist_active(self.process_group):
+            return
+        import torch.distributed as dist
+        gsrc = dist.get_global_rank(self.process_group, src) if self.process_group is not None else src
+        for t in (self.codebook.data, self.ema_cnt, self.ema_sum, self.usage_total, self.steps_since_used,
+                  self.last_perplexity, self.n_dead):
+            dist.broadcast(t, src=gsrc, group=self.process_group)
+        self._shadow_key = None
+
     # ------------------------------------------------------------------ scratch management
     def _search_for(self, dtype: torch.dtype) -> str:
         """"auto": half-precision latents (bf16, and fp16 -- the reference script's default autocast dtype,
-        scripts/train_vqvae.py:284-286) take the tensor-core search, fp32 latents the fp32 search."""
+        scripts/train_vqvae.py:284-286) take the tensor-core search, fp32 latents the fp32 search.  An emb_dim the
+        tensor-core kernel cannot take (not a multiple of 8, below 8 or above 512) goes to the fp32 kernel, which has no
+        shape limits; only an explicit search="bf16" insists (and raises for such a shape)."""
         if self.search != "auto":
             return self.search
+        D = self.emb_dim
+        if D % 8 != 0 or D < 8 or D > 512:
+            return "fp32"
         return "bf16" if dtype in (torch.bfloat16, torch.float16) else "fp32"
 
     def _ensure_shadow(self, search: str) -> None:
@@ -290,7 +314,8 @@ class VectorQuantizer(nn.Module):
             self.peer_exchange = "nccl"
             return False
         K, D = self.codebook_size, self.emb_dim
-        self._peers = parallel.PeerExchange(K * D + K, self.codebook.device, self.process_group)
+        self._peers = parallel.PeerExchange(K * D + K, self.codebook.device, self.process_group,
+                                            timeout_s=self.peer_timeout_s)
         return True
 
     def _stats_buffer(self) -> torch.Tensor:
@@ -435,6 +460,11 @@ class VectorQuantizer(nn.Module):
         if not z.is_cuda:
             raise RuntimeError("VectorQuantizer.forward needs a CUDA tensor: the kernels are sm_100a only and "
                                "there is no CPU fallback (attribute access and state_dict work on CPU)")
+        if z.device.index != torch.cuda.current_device():
+            # launches, streams, graph capture and scratch allocation all follow the tensor's device, not whatever
+            # device the calling thread has selected
+            with torch.cuda.device(z.device):
+                return self.forward(z)
         if self.channel_first:
             return self._forward_channel_first(z)
         if z.shape[-1] != self.emb_dim:
@@ -482,6 +512,9 @@ class VectorQuantizer(nn.Module):
         dev = self.codebook.device
         if dev.type != "cuda":
             raise RuntimeError("VectorQuantizer.forward_host: the module must live on a CUDA device (no CPU fallback)")
+        if dev.index != torch.cuda.current_device():
+            with torch.cuda.device(dev):
+                return self.forward_host(z_host, chunks)
         lead, D, K = z_host.shape[:-1], self.emb_dim, self.codebook_size
         zh = z_host.reshape(-1, D)
         if not zh.is_contiguous():
