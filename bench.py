@@ -4,16 +4,24 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1|c2|c3|c4|c5] [--impl native|reference]
 
 One "step" = one pass of the hot path over one batch of synthetic latents: nearest-code search (a-1),
-fused gather / straight-through / loss / code statistics pass (a-2..a-5), code-stat all-reduce when N > 1
+fused gather / straight-through / loss / code statistics pass (a-2..a-5), code-stat exchange when N > 1
 (a-6), EMA codebook update + usage + perplexity (a-7..a-9) -- i.e. VectorQuantizer.forward in training mode,
 quantizer="ema".  Workloads:
-    c2 (default, BASELINE configs[1]): N = 256*5*32*32 = 1 310 720 vectors/GPU, K=1024, D=128, bf16
-    c4 (BASELINE configs[3])          : N = 524 288 vectors/GPU, K=8192, D=256, bf16
+    c4 (default, BASELINE configs[3]) : N = 524 288 vectors/GPU (4 194 304 per 8-GPU step), K=8192, D=256, bf16 --
+                                        the configuration north_star's >= 70 % tensor / >= 75 % HBM / near-linear
+                                        8-GPU targets are quoted on
+    c2 (BASELINE configs[1])          : N = 256*5*32*32 = 1 310 720 vectors/GPU, K=1024, D=128, bf16 (carried as the
+                                        second record `c2` of the default line)
     c1 (BASELINE configs[0])          : N = 40 960, K=512, D=64 (the reference-scale case)
     c3 (BASELINE configs[2])          : type/phase split, two codebooks K=2048 D=128 (262 144 + 1 310 720 vectors/GPU)
     c5 (BASELINE configs[4])          : the batch-2048 step's quantiser load, 10 485 760 vectors/GPU, K=8192, D=256
 Weak scaling: every rank runs the same per-GPU workload on its own shard; `value` is the whole-job rate.
-Prints ONE JSON line on rank 0.
+Prints ONE JSON line on rank 0.  Keys beyond the base contract: `roofline` (search vs the measured bf16 burst peak),
+`roofline_pass` (scatter + pass vs the measured HBM copy peak), `cpu_baseline`, `e2e` (training-step contract: latents
+host -> device, loss + perplexity back), `e2e_full` (latents in, quantised rows + indices back to pinned host memory),
+`c2` (the same measurements on BASELINE configs[1]), `sustained` (ms/step over a >= 2 s loop with its own clock
+record), `gpu_eager` (the same step in stock PyTorch ops on the same GPU), `fp32_tier` (the 1e-5 search tier at this
+workload), `dp_check` (N > 1: replicas bit-identical, rows counted).
 """
 from __future__ import annotations
 
@@ -36,11 +44,14 @@ WORKLOADS = {
     "c2": dict(N=256 * 5 * 32 * 32, K=1024, D=128, desc="C2: batch 256 of 5x32x32 latents, K=1024 D=128, bf16 fwd+EMA"),
     "c3": dict(N=256 * 5 * 32 * 32, N_type=256 * 32 * 32, K=2048, D=128,
                desc="C3: type/phase split, two codebooks K=2048 D=128; type 262144 + phase 1310720 vectors per step"),
-    "c4": dict(N=524288, K=8192, D=256, desc="C4: K=8192 D=256, 524288 vectors per GPU (4M per 8-GPU step)"),
+    "c4": dict(N=524288, K=8192, D=256, desc="C4: K=8192 D=256, 524288 vectors per GPU (4M per 8-GPU step), bf16 fwd+EMA"),
     "c5": dict(N=2048 * 5120, K=8192, D=256, desc="C5: quantiser load of the batch-2048 step, 10485760 vectors, K=8192 D=256"),
 }
 METRIC = "quantised latent vectors/sec (VQ fwd+EMA)"
 UNIT = "vectors/s"
+CPU_SAMPLE = 32768          # vectors per step of the CPU legs (cpu_baseline AND --impl reference: one sample size)
+TRAFFIC_SOURCE = "profiles/traffic.json (dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full capture " \
+                 "committed with the profiles; not re-measured in this run)"
 
 
 def load_traffic(workload_key, kernel):
@@ -77,9 +88,10 @@ class ClockSampler:
                                           "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
-            return
+            return self
         self.thr = threading.Thread(target=self._read, daemon=True)
         self.thr.start()
+        return self
 
     def _read(self):
         for line in self.proc.stdout:
@@ -122,6 +134,7 @@ def make_inputs(wl, rank, device, dtype=torch.bfloat16, data="gaussian"):
     return z.to(dtype), E
 
 
+# ------------------------------------------------------------------------------------------------ CPU legs (oracle)
 def oracle_step(R, z, E, state, K):
     """The same step on the CPU oracle (fp32 eager torch, chunked so the [chunk, K] matrix stays small)."""
     idx, _ = R.assign(z, E, "fp32", chunk=8192)
@@ -134,19 +147,22 @@ def oracle_step(R, z, E, state, K):
     return En, q, sq
 
 
+def cpu_inputs(wl):
+    sample = min(wl["N"], CPU_SAMPLE)
+    z = torch.randn(sample, wl["D"], generator=torch.Generator().manual_seed(1234))
+    E = torch.randn(wl["K"], wl["D"], generator=torch.Generator().manual_seed(4321))
+    return sample, z, E, {"n": torch.ones(wl["K"]), "m": E.clone()}
+
+
 def cpu_baseline(wl, target_seconds=12.0):
     """Oracle ("port") on the host cores, on a bounded sample of the same workload."""
     from oracle import vq_reference as R
     torch.set_num_threads(os.cpu_count() or 1)
-    sample = min(wl["N"], 65536)
-    g = torch.Generator().manual_seed(1234)
-    z = torch.randn(sample, wl["D"], generator=g)
-    E = torch.randn(wl["K"], wl["D"], generator=torch.Generator().manual_seed(4321))
-    state = {"n": torch.ones(wl["K"]), "m": E.clone()}
+    sample, z, E, state = cpu_inputs(wl)
     oracle_step(R, z[:4096], E, dict(state), wl["K"])          # warm-up
     t0 = time.perf_counter(); reps = 0
     while True:
-        E2, _, _ = oracle_step(R, z, E, state, wl["K"])
+        oracle_step(R, z, E, state, wl["K"])
         reps += 1
         if time.perf_counter() - t0 > target_seconds or reps >= 50:
             break
@@ -158,16 +174,13 @@ def cpu_baseline(wl, target_seconds=12.0):
 
 def run_reference(args, wl):
     """--impl reference: the reference tree has NO quantiser source, so the reference arm is the
-    CPU oracle port, all host threads, each step a bounded sample of the workload."""
+    CPU oracle port, all host threads, each step a bounded sample of the workload (the same sample cpu_baseline takes)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import vq_reference as R
     torch.set_num_threads(os.cpu_count() or 1)
-    sample = min(wl["N"], 32768)
-    z = torch.randn(sample, wl["D"], generator=torch.Generator().manual_seed(1234))
-    E = torch.randn(wl["K"], wl["D"], generator=torch.Generator().manual_seed(4321))
-    state = {"n": torch.ones(wl["K"]), "m": E.clone()}
+    sample, z, E, state = cpu_inputs(wl)
     for _ in range(args.warmup):
         oracle_step(R, z, E, state, wl["K"])
     t0 = time.perf_counter()
@@ -186,6 +199,7 @@ def run_reference(args, wl):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------ native arm
 def time_kernel(fn, iters, flush):
     """Average device time of one launch group, CUDA events on the launching (current) stream, L2 flushed between."""
     evs = []
@@ -198,27 +212,62 @@ def time_kernel(fn, iters, flush):
     return sum(a.elapsed_time(b) for a, b in evs) / len(evs)
 
 
-def run_native(args, wl):
-    import torch.distributed as dist
-    from vqvae_b200 import VectorQuantizer, ops
-    from vqvae_b200._lib import VQ_STAT_SUM_Z
+class Ctx:
+    """Process-wide state of one bench run (rank, device, peaks, L2 flush buffer, barrier)."""
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py (native arm) needs a CUDA device; there is no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    N, K, D = wl["N"], wl["K"], wl["D"]
-    z, E = make_inputs(wl, rank, dev, data=args.data)
-    mod = VectorQuantizer(D, K, beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5).to(dev)
+    def __init__(self):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py (native arm) needs a CUDA device; there is no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.numa = None
+        if self.world > 1:
+            from vqvae_b200 import parallel
+            self.numa = parallel.pin_to_gpu_numa(self.local)      # before any pinned allocation (first touch)
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.peaks = load_peaks()
+        self.flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)      # > 126 MB L2
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, ms: float) -> float:
+        t = torch.tensor([ms], device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t)
+
+    def flush(self):
+        self.flush_buf.fill_(1)
+
+
+def build_module(ctx, wl, E, args):
+    from vqvae_b200 import VectorQuantizer
+    mod = VectorQuantizer(wl["D"], wl["K"], beta=0.25, quantizer="ema", ema_decay=0.99, ema_eps=1e-5).to(ctx.dev)
     with torch.no_grad():
         mod.codebook.copy_(E); mod.ema_sum.copy_(E)
-    mod.train()
-    n_type = wl.get("N_type", 0)           # C3: a second codebook for the type stream, run underneath the phase stream
+    return mod.train()
+
+
+def measure(ctx, key, args, steps, warmup, full=True, clocks=True):
+    """One workload: `value` (latents resident in HBM), per-kernel rooflines (rank 0) and -- full -- the host-buffer
+    numbers.  Returns (record, module, rows this rank pushed through the module)."""
+    from vqvae_b200 import ops
+    from vqvae_b200._lib import VQ_STAT_SUM_Z
+    wl = WORKLOADS[key]
+    dev, world, rank = ctx.dev, ctx.world, ctx.rank
+    N, K, D = wl["N"], wl["K"], wl["D"]
+    z, E = make_inputs(wl, rank, dev, data=args.data)
+    mod = build_module(ctx, wl, E, args)
+    rows_done = 0
+    n_type = wl.get("N_type", 0)           # C3: a second codebook for the type stream
     split = None
     if n_type:
         from vqvae_b200 import SplitQuantizer
@@ -229,72 +278,94 @@ def run_native(args, wl):
             split.quant_type.codebook.copy_(E.flip(0)); split.quant_type.ema_sum.copy_(E.flip(0))
         split.train()
         z_type = z[:n_type].clone()
-    peaks = load_peaks()
-    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     def step_resident():
         with torch.no_grad():
             return split(z_type, z) if split is not None else mod(z)
 
-    # ---------------- value: inputs resident in HBM (335 MB of latents per step at c2 -- larger than L2)
-    for _ in range(args.warmup):
+    # ---------------- value: inputs resident in HBM, larger than L2 (268 MB of latents per step at c4, 336 MB at c2)
+    for _ in range(warmup):
         step_resident()
-    barrier()
-    clocks = ClockSampler(local); clocks.start()
+    rows_done += warmup * N
+    ctx.barrier()
+    sampler = ClockSampler(ctx.local).start() if clocks else None
     l0 = ops.launch_count() + mod.graph_launches        # eager launches + launches replayed inside CUDA graphs
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         step_resident()
     e1.record()
-    barrier()
+    ctx.barrier()
+    rows_done += steps * N
     launches = ops.launch_count() + mod.graph_launches - l0
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms)
+    ms_total = ctx.max_over_ranks(e0.elapsed_time(e1))
+    n_total = (N + n_type) * world
+    rec = {"value": n_total * steps / (ms_total * 1e-3), "ms_per_step": ms_total / steps, "gpu_launches": int(launches)}
 
     # ---------------- e2e: HOST buffers through the public module call, H2D + D2H inside the timed region
-    z_host = z.cpu().pin_memory()
-    res_host = torch.empty(2, dtype=torch.float32).pin_memory()
+    if full:
+        z_host = z.cpu().pin_memory()
+        res_host = torch.empty(2, dtype=torch.float32).pin_memory()
+        if split is not None:
+            zt_host = z_type.cpu().pin_memory()
 
-    if split is not None:
-        zt_host = z_type.cpu().pin_memory()
+        def step_e2e():
+            with torch.no_grad():
+                if split is not None:
+                    split.forward_host(zt_host, z_host)
+                    loss = split.loss
+                else:                       # public host entry: row chunks cross PCIe while the previous chunk is quantised
+                    _, loss, _ = mod.forward_host(z_host)
+            res_host[0:1].copy_(loss.reshape(1), non_blocking=True)
+            res_host[1:2].copy_(mod.last_perplexity, non_blocking=True)
+            torch.cuda.current_stream().synchronize()             # the caller reads the step's result
 
-    def step_e2e():
-        with torch.no_grad():
-            if split is not None:
-                split.forward_host(zt_host, z_host)
-                loss = split.loss
-            else:                       # public host entry: row chunks cross PCIe while the previous chunk is quantised
-                q, loss, idx = mod.forward_host(z_host)
-        res_host[0:1].copy_(loss.reshape(1), non_blocking=True)
-        res_host[1:2].copy_(mod.last_perplexity, non_blocking=True)
-        torch.cuda.current_stream().synchronize()             # the caller reads the step's result
+        def timed(fn, n):
+            ctx.barrier()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record()
+            for _ in range(n):
+                fn()
+            f1.record()
+            ctx.barrier()
+            return ctx.max_over_ranks(f0.elapsed_time(f1))
 
-    for _ in range(max(1, args.warmup // 2)):
-        step_e2e()
-    barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    for _ in range(args.steps):
-        step_e2e()
-    f1.record()
-    barrier()
-    clk = clocks.stop()
-    ems = torch.tensor([f0.elapsed_time(f1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ems, op=dist.ReduceOp.MAX)
-    e2e_ms = float(ems)
+        for _ in range(max(1, warmup // 2)):
+            step_e2e()
+        e2e_ms = timed(step_e2e, steps)
+        rows_done += (max(1, warmup // 2) + steps) * N
+        rec["e2e"] = {"value": n_total * steps / (e2e_ms * 1e-3), "unit": UNIT,
+                      "h2d_bytes_per_step": (N + n_type) * D * 2, "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / steps,
+                      "what": "training-step contract (scripts/train_vqvae.py:275-347): latents host -> device, loss + "
+                              "perplexity back; quantised rows and indices stay on the device for the decoder"}
+        if split is None:
+            q_host = torch.empty_like(z_host)
+            i_host = torch.empty(N, dtype=torch.int64).pin_memory()
+
+            def step_e2e_full():
+                with torch.no_grad():
+                    _, loss, _ = mod.forward_host(z_host, q_host=q_host, idx_host=i_host)
+                res_host[0:1].copy_(loss.reshape(1), non_blocking=True)
+                res_host[1:2].copy_(mod.last_perplexity, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+
+            step_e2e_full()
+            nfull = max(5, steps // 2)
+            full_ms = timed(step_e2e_full, nfull)
+            rows_done += (1 + nfull) * N
+            rec["e2e_full"] = {"value": N * world * nfull / (full_ms * 1e-3), "unit": UNIT,
+                               "h2d_bytes_per_step": N * D * 2, "d2h_bytes_per_step": N * D * 2 + N * 8 + 8,
+                               "ms_per_step": full_ms / nfull,
+                               "what": "latents in, quantised rows + int64 indices + loss + perplexity back to pinned host "
+                                       "memory (results stream back chunk by chunk under the remaining chunks)"}
+            del q_host, i_host
+        del z_host
+    if sampler is not None:
+        rec["clocks"] = sampler.stop()
 
     # ---------------- per-kernel timing for the roofline (rank 0, timed alone, L2 flushed between launches)
-    line_extra = {}
     if rank == 0:
+        peaks = ctx.peaks
         Eb, nrm = mod._E_bf16, mod._e_norm2
         # private zero-filled workspace under the same contract the module uses (VQ_SEARCH_WS_CLEAN)
         ws = torch.zeros(ops.workspace_bytes(N, K, D, z.dtype), dtype=torch.uint8, device=dev)
@@ -304,47 +375,174 @@ def run_native(args, wl):
         stats = torch.empty(K * D + K, dtype=torch.float32, device=dev)   # private: never the module's exchange buffer
         csum, ccnt = stats[:K * D].view(K, D), stats[K * D:]
         Ec = mod.codebook.detach()
-        flush = lambda: flush_buf.fill_(1)
-        it = max(5, min(20, args.steps))
+        it = max(5, min(20, steps))
         # the pairing the module runs: the search leaves the counting-sort inputs in ws, the pass group picks them up
         t_assign = time_kernel(lambda: ops.assign(z, Ec, Eb, nrm, "bf16", idx, None, ws, presort=True, ws_clean=True),
-                               it, flush)
+                               it, ctx.flush)
         t_pass = time_kernel(lambda: ops.gather_st_loss_scatter(z, idx, Ec, q, sq, ccnt, csum, VQ_STAT_SUM_Z, False, ws,
-                                                                presorted=True), it, flush)
+                                                                presorted=True), it, ctx.flush)
         flops = 2.0 * N * K * D                                   # 2*K*D per vector
         pass_bytes = N * (D * 2 + 4 + D * 2) + K * D * 4 * 2 + K * 4   # read z + idx, write q; codebook + stats once
         tf = flops / (t_assign * 1e-3) / 1e12
         gbs = pass_bytes / (t_pass * 1e-3) / 1e9
-        line_extra["roofline"] = {"kernel": "assign_tc_kernel (a-1, tcgen05; incl. the histogram / rank / scan by-product)", "bound": "tensor", "achieved": tf,
-                                  "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": tf / peaks["tf_burst"],
-                                  "traffic": load_traffic(args.workload, "assign_tc_kernel"),
-                                  "algorithmic_bytes": N * (D * 2 + 4) + K * D * 2 + K * 4,
-                                  "peak_source": peaks["src"] + " burst (kernel timed alone)",
-                                  "ms_per_launch": t_assign}
-        line_extra["roofline_pass"] = {"kernel": "scatter_ranked_kernel + pass_kernel (a-2..a-5; histogram / ranks / scan come from the search kernel)", "bound": "hbm",
-                                       "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
-                                       "traffic": load_traffic(args.workload, "pass_group"),
-                                       "algorithmic_bytes": pass_bytes, "peak_source": peaks["src"],
-                                       "ms_per_launch": t_pass}
-        line_extra["cpu_baseline"] = cpu_baseline(wl) if (world == 1 and not args.skip_cpu) else None
+        rec["roofline"] = {"kernel": "assign_tc_kernel (a-1, tcgen05; incl. the histogram / rank / scan by-product)",
+                           "bound": "tensor", "achieved": tf, "peak": peaks["tf_burst"], "unit": "TFLOP/s",
+                           "frac": tf / peaks["tf_burst"], "frac_of_sustained_peak": tf / peaks["tf_sust"],
+                           "traffic": load_traffic(key, "assign_tc_kernel"), "traffic_source": TRAFFIC_SOURCE,
+                           "algorithmic_bytes": N * (D * 2 + 4) + K * D * 2 + K * 4,
+                           "peak_source": peaks["src"] + " burst (kernel timed alone)", "ms_per_launch": t_assign}
+        rec["roofline_pass"] = {"kernel": "scatter_ranked_kernel + pass_kernel (a-2..a-5; histogram / ranks / scan come "
+                                          "from the search kernel)", "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"],
+                                "unit": "GB/s", "frac": gbs / peaks["hbm"], "traffic": load_traffic(key, "pass_group"),
+                                "traffic_source": TRAFFIC_SOURCE, "algorithmic_bytes": pass_bytes,
+                                "peak_source": peaks["src"], "ms_per_launch": t_pass}
+        del ws, idx, q, stats
+    return rec, mod, z, rows_done
 
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    if rank != 0:
-        return
-    n_total = (N + n_type) * world
-    line = {"metric": METRIC, "value": n_total * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+
+def sustained(ctx, mod, z, seconds=2.0):
+    """The resident step back to back for >= `seconds` (burst clocks decay to the power-capped steady state)."""
+    N = z.shape[0]
+    with torch.no_grad():
+        for _ in range(3):
+            mod(z)
+    ctx.barrier()
+    sampler = ClockSampler(ctx.local).start()
+    # the loop length is fixed up front (same on every rank): a first short run sizes it
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    with torch.no_grad():
+        for _ in range(20):
+            mod(z)
+    e1.record()
+    torch.cuda.synchronize()
+    est = ctx.max_over_ranks(e0.elapsed_time(e1)) / 20
+    steps = int(min(20000, max(50, seconds * 1e3 / max(est, 1e-3))))
+    ctx.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    with torch.no_grad():
+        for _ in range(steps):
+            mod(z)
+    e1.record()
+    ctx.barrier()
+    ms = ctx.max_over_ranks(e0.elapsed_time(e1))
+    clk = sampler.stop()
+    return {"ms_per_step": ms / steps, "value": N * ctx.world * steps / (ms * 1e-3), "unit": UNIT, "steps": steps,
+            "seconds": ms * 1e-3, "clocks": clk}, (23 + steps) * N
+
+
+def gpu_eager(key):
+    """The same step in stock PyTorch ops on this GPU (tools/bench_eager_gpu.py): what a user gets without the library."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_eager_gpu
+    return bench_eager_gpu.run(key, WORKLOADS[key], make_inputs)
+
+
+def fp32_tier(ctx, key, mod, z, iters=5):
+    """The 1e-5 search tier (search="fp32") on this workload's shape: fp32 latents, search kernel timed alone."""
+    from vqvae_b200 import ops
+    wl = WORKLOADS[key]
+    N, K, D = wl["N"], wl["K"], wl["D"]
+    dev = ctx.dev
+    zf = z.float()
+    E = mod.codebook.detach()
+    Eb = torch.empty((K, D), dtype=torch.bfloat16, device=dev)
+    nrm = torch.empty(ops.norm_elems(K), dtype=torch.float32, device=dev)
+    out = {}
+    try:
+        ops.prepare_codebook(E, "fp32", Eb, nrm)
+        ws = torch.zeros(ops.workspace_bytes(N, K, D, zf.dtype), dtype=torch.uint8, device=dev)
+        idx = torch.empty(N, dtype=torch.int32, device=dev)
+        fn = lambda: ops.assign(zf, E, Eb, nrm, "fp32", idx, None, ws, presort=True, ws_clean=True)
+        fn(); torch.cuda.synchronize()
+        t = time_kernel(fn, iters, ctx.flush)
+        tf = 2.0 * N * K * D / (t * 1e-3) / 1e12
+        out = {"ms_per_launch": t, "algorithmic_tflops": tf, "latents": "fp32",
+               "note": "search='fp32' (1e-5 tier) timed alone, 2*N*K*D algorithmic flops"}
+    except Exception as exc:                       # never fail the headline because of the side record
+        out = {"error": str(exc)[:300]}
+    return out
+
+
+def run_native(args):
+    ctx = Ctx()
+    key = args.workload
+    wl = WORKLOADS[key]
+    rec, mod, z, rows = measure(ctx, key, args, args.steps, args.warmup, full=True)
+    extras = {}
+    if not args.no_extras:
+        if key in ("c2", "c4") :
+            srec, n = sustained(ctx, mod, z)
+            rows += n
+            extras["sustained"] = srec
+    # ---------------- multi-GPU correctness the driver can see
+    if ctx.world > 1:
+        from vqvae_b200 import parallel
+        dp = {"replicas_identical": False, "rows_counted": None, "rows_expected": None, "exchange": mod.peer_exchange
+              if mod._peers is None else "peer"}
+        try:
+            parallel.assert_replicas_identical(mod.codebook)
+            dp["replicas_identical"] = True
+        except RuntimeError as exc:
+            dp["error"] = str(exc)
+        tot = torch.tensor([rows], dtype=torch.int64, device=ctx.dev)
+        ctx.dist.all_reduce(tot)
+        dp["rows_expected"] = int(tot)
+        dp["rows_counted"] = int(mod.usage_total.sum())
+        dp["ok"] = dp["replicas_identical"] and dp["rows_counted"] == dp["rows_expected"]
+        extras["dp_check"] = dp
+    else:
+        extras["dp_check"] = "skipped: 1 GPU"
+        assert int(mod.usage_total.sum()) == rows, "usage_total does not add up to the rows quantised"
+    if mod._peers is not None:
+        mod._peers.close()
+    if not args.no_extras and key == "c4":
+        if ctx.rank == 0:
+            extras["fp32_tier"] = fp32_tier(ctx, key, mod, z)
+        del mod, z
+        torch.cuda.empty_cache()
+        c2rec, c2mod, c2z, _ = measure(ctx, "c2", args, args.steps, args.warmup, full=(ctx.world == 1), clocks=False)
+        c2rec["config"] = {"workload": WORKLOADS["c2"]["desc"], "N_per_gpu": WORKLOADS["c2"]["N"], "K": 1024, "D": 128}
+        c2rec["unit"] = UNIT
+        if ctx.world == 1:
+            s2, _ = sustained(ctx, c2mod, c2z)
+            c2rec["sustained"] = s2
+        if c2mod._peers is not None:
+            c2mod._peers.close()
+        extras["c2"] = c2rec
+        del c2mod, c2z
+        torch.cuda.empty_cache()
+    if ctx.rank == 0 and ctx.world == 1 and not args.no_extras and key in ("c2", "c4"):
+        try:
+            extras["gpu_eager"] = {key: gpu_eager(key)}
+            if key == "c4":
+                extras["gpu_eager"]["c2"] = gpu_eager("c2")
+        except Exception as exc:
+            extras["gpu_eager"] = {"error": str(exc)[:300]}
+    if ctx.rank == 0:
+        extras["cpu_baseline"] = cpu_baseline(wl) if (ctx.world == 1 and not args.skip_cpu) else None
+    dp_ok = True
+    if ctx.world > 1:
+        dp_ok = bool(extras["dp_check"]["ok"])
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
+    if ctx.rank != 0:
+        sys.exit(0 if dp_ok else 3)
+    N, K, D = wl["N"], wl["K"], wl["D"]
+    line = {"metric": METRIC, "value": rec.pop("value"), "unit": UNIT, "n_gpus": ctx.world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": rec.pop("ms_per_step"), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic" if args.data == "gaussian" else "synthetic (trained-like: Zipf(1.1) code usage, sigma 0.1)",
-            "config": {"workload": wl["desc"], "N_per_gpu": N + n_type, "K": K, "D": D, "quantizer": "ema",
-                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (%.0f MB of latents per step)" % (N * D * 2 / 1e6)},
-            "e2e": {"value": n_total * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (N + n_type) * D * 2,
-                    "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": int(launches), "clocks": clk}
-    line.update(line_extra)
+            "config": {"workload": wl["desc"], "N_per_gpu": N + wl.get("N_type", 0), "K": K, "D": D, "quantizer": "ema",
+                       "parallelism": f"dp{ctx.world}", "numa": ctx.numa,
+                       "l2": "inputs larger than L2 (%.0f MB of latents per step)" % (N * D * 2 / 1e6)},
+            "headline_e2e": "e2e (training-step contract); e2e_full also returns quantised rows and indices to the host"}
+    line.update(rec)
+    line.update(extras)
     print(json.dumps(line), flush=True)
+    if not dp_ok:
+        sys.exit(3)
 
 
 def main():
@@ -352,18 +550,19 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c4")
     ap.add_argument("--impl", choices=["native", "reference"], default="native")
     ap.add_argument("--data", choices=["gaussian", "trained"], default="gaussian",
                     help="synthetic latents: N(0,1) (default) or trained-like (Zipf-skewed codes + noise)")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="only the base line of the chosen workload (no c2 record, sustained, gpu_eager, fp32_tier)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
-    wl = WORKLOADS[args.workload]
     if args.impl == "reference":
-        run_reference(args, wl)
+        run_reference(args, WORKLOADS[args.workload])
     else:
-        run_native(args, wl)
+        run_native(args)
 
 
 if __name__ == "__main__":

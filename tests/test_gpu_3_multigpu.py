@@ -1,5 +1,6 @@
-"""a-6 on real GPUs (needs >= 2 devices; skipped on a single-GPU box): the fused peer-memory exchange
-(vq_ema_update_dp over CUDA IPC) against the NCCL all-reduce path, ragged shards, replicas bit-identical."""
+"""a-6 on real GPUs (needs >= 2 devices; on a single-GPU box the test skips and `bench.py --gpus N` carries the
+driver-visible `dp_check`): data-parallel steps against the oracle on the concatenated batch for both exchanges
+(fused peer-memory path over CUDA IPC, NCCL all-reduce), ragged shards, per-rank init seeds, replicas bit-identical."""
 import os
 import subprocess
 import sys
@@ -19,3 +20,4 @@ def test_peer_exchange_matches_nccl_two_ranks():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=280)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert out.stdout.count("-> OK") == 3 and "MISMATCH" not in out.stdout
+    assert '"ok": true' in out.stdout

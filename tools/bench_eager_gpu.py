@@ -13,7 +13,6 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from bench import WORKLOADS, make_inputs  # noqa: E402
 
 
 @torch.no_grad()
@@ -40,26 +39,30 @@ def eager_step(z, E, ema_cnt, ema_sum, decay=0.99, eps=1e-5, beta=0.25, chunk=65
     return q, loss, idx, perplexity
 
 
+def run(name, wl, make_inputs, iters=10):
+    """bench.py's `gpu_eager` record for one workload (current CUDA device)."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    z, E = make_inputs(wl, 0, dev)
+    E = E.to(dev)
+    ema_cnt, ema_sum = torch.ones(wl["K"], device=dev), E.clone()
+    for _ in range(3):
+        eager_step(z, E, ema_cnt, ema_sum)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        eager_step(z, E, ema_cnt, ema_sum)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    return {"impl": "torch eager ops on the same B200 (chunked bf16 matmul + argmin, index_select, index_add_)",
+            "workload": wl["desc"], "ms_per_step": ms, "vectors_per_s": wl["N"] / (ms * 1e-3)}
+
+
 def main():
-    dev = torch.device("cuda:0")
+    from bench import WORKLOADS, make_inputs
     for name in sys.argv[1:] or ["c2", "c4"]:
-        wl = WORKLOADS[name]
-        z, E = make_inputs(wl, 0, dev)
-        E = E.to(dev)
-        ema_cnt, ema_sum = torch.ones(wl["K"], device=dev), E.clone()
-        for _ in range(3):
-            eager_step(z, E, ema_cnt, ema_sum)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        iters = 10
-        e0.record()
-        for _ in range(iters):
-            eager_step(z, E, ema_cnt, ema_sum)
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / iters
-        print(json.dumps({"impl": "torch eager on the same B200", "workload": wl["desc"], "ms_per_step": ms,
-                          "vectors_per_s": wl["N"] / (ms * 1e-3)}), flush=True)
+        print(json.dumps(run(name, WORKLOADS[name], make_inputs)), flush=True)
 
 
 if __name__ == "__main__":

@@ -19,6 +19,36 @@ def shard_bounds(n_rows: int, rank: int, world: int) -> Tuple[int, int]:
     return a, a + base + (1 if rank < rem else 0)
 
 
+def pin_to_gpu_numa(local_rank: int):
+    """Bind this process (and the pinned host memory it allocates from now on: first touch) to the CPUs of the NUMA node
+    its GPU hangs off, so that eight ranks staging batches through pinned memory do not all pull from node 0.  Reads
+    the PCI bus id from CUDA and the node from sysfs; returns a short description, or None when nothing could be done
+    (no sysfs entry, node -1, a container without the cpulist).  Call before the first pinned allocation."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = torch.cuda.get_device_properties(local_rank).pci_domain_id
+        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        with open(path) as fh:
+            node = int(fh.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as fh:
+            spec = fh.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return f"gpu {local_rank} -> numa node {node} ({len(cpus)} cpus)"
+    except Exception:
+        return None
+
+
 def dist_active(group=None) -> bool:
     return dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
 

@@ -493,9 +493,13 @@ class VectorQuantizer(nn.Module):
             return q.reshape(*lead, self.emb_dim), loss, idx.reshape(lead)
 
     @torch.no_grad()
-    def forward_host(self, z_host: torch.Tensor, chunks: Optional[int] = None):
+    def forward_host(self, z_host: torch.Tensor, chunks: Optional[int] = None, q_host: Optional[torch.Tensor] = None,
+                     idx_host: Optional[torch.Tensor] = None):
         """Quantise a batch that lives in (pinned) HOST memory: `[..., D]` CPU tensor in, device tensors
-        `(quantized, loss, indices)` out.  The batch is cut into row chunks; chunk c + 1 crosses PCIe on a copy stream
+        `(quantized, loss, indices)` out.  With `q_host` / `idx_host` (pinned CPU tensors of the output shapes: the
+        latents' dtype and int64) the results also travel BACK, chunk by chunk on a third stream while later chunks are
+        still being copied in and quantised (PCIe is full duplex), and those host tensors are returned in place of the
+        device ones -- valid once the current stream has been synchronised.  The batch is cut into row chunks; chunk c + 1 crosses PCIe on a copy stream
         while the kernels work on chunk c (the search per chunk, the gather / loss / statistics pass accumulating
         across chunks with VQ_STAT_ACCUMULATE), then one EMA update for the whole batch -- the same arithmetic as
         `forward` on the copied tensor, with the transfer hidden behind the compute instead of in front of it.
@@ -509,6 +513,9 @@ class VectorQuantizer(nn.Module):
         search = self._search_for(z_host.dtype)
         if z_host.dtype not in (torch.bfloat16, torch.float32):
             z_host = z_host.to(torch.float32)
+        for name, t, dt in (("q_host", q_host, z_host.dtype), ("idx_host", idx_host, torch.int64)):
+            if t is not None and (t.is_cuda or t.dtype != dt or not t.is_contiguous() or not t.is_pinned()):
+                raise ValueError(f"forward_host: {name} must be a contiguous pinned CPU tensor of dtype {dt}")
         dev = self.codebook.device
         if dev.type != "cuda":
             raise RuntimeError("VectorQuantizer.forward_host: the module must live on a CUDA device (no CPU fallback)")
@@ -528,6 +535,12 @@ class VectorQuantizer(nn.Module):
             q, loss, idx64, _ = self._run_step(zh.to(dev, non_blocking=True), search)
             if q.dtype != z_host.dtype:
                 q = q.to(z_host.dtype)
+            if q_host is not None:
+                q_host.view(-1, D).copy_(q, non_blocking=True)
+                q = q_host
+            if idx_host is not None:
+                idx_host.view(-1).copy_(idx64, non_blocking=True)
+                idx64 = idx_host
             return q.reshape(*lead, D), loss.reshape(()), idx64.reshape(lead)
         if chunks is None:                      # ~128 K rows per chunk: transfer time per chunk well above launch costs
             chunks = max(1, min(16, N // 131072))
@@ -550,6 +563,13 @@ class VectorQuantizer(nn.Module):
         E = self.codebook.detach()
         kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
         copy.wait_stream(cur)                   # the fresh device buffers are not reused memory still in flight
+        back = None
+        if (q_host is not None or idx_host is not None) and N > 0:
+            if getattr(self, "_back_stream", None) is None or self._back_stream.device != dev:
+                self._back_stream = torch.cuda.Stream(device=dev)
+            back = self._back_stream
+            qh2 = q_host.view(-1, D) if q_host is not None else None
+            ih1 = idx_host.view(-1) if idx_host is not None else None
         landed = []
         with torch.cuda.stream(copy):
             for a, b in bounds:
@@ -563,11 +583,26 @@ class VectorQuantizer(nn.Module):
             ops.gather_st_loss_scatter(z_dev[a:b], idx32[a:b], E, q[a:b], sqerr, code_cnt, code_sum, kind,
                                        self.deterministic, ws, accumulate=c > 0, idx64_out=idx64[a:b], loss_out=loss,
                                        loss_scale=self._loss_scale(N), presorted=True)
+            if back is not None:                # this chunk's results go home under the next chunk's kernels
+                back.wait_stream(cur)
+                with torch.cuda.stream(back):
+                    if qh2 is not None:
+                        qh2[a:b].copy_(q[a:b], non_blocking=True)
+                    if ih1 is not None:
+                        ih1[a:b].copy_(idx64[a:b], non_blocking=True)
         if not bounds:
             ops.gather_st_loss_scatter(z_dev, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws,
                                        idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N))
         z_dev.record_stream(copy)
         self._finish_step(code_cnt, code_sum, search, ws)
+        if back is not None:
+            q.record_stream(back)
+            idx64.record_stream(back)
+            cur.wait_stream(back)               # synchronising the caller's stream makes the host tensors valid
+            if q_host is not None:
+                q = q_host
+            if idx_host is not None:
+                idx64 = idx_host
         if q.dtype != z_host.dtype:
             q = q.to(z_host.dtype)
         return q.reshape(*lead, D), loss.reshape(()), idx64.reshape(lead)
