@@ -339,7 +339,7 @@ def measure(ctx, key, args, steps, warmup, full=True, clocks=True):
                       "what": "training-step contract (scripts/train_vqvae.py:275-347): latents host -> device, loss + "
                               "perplexity back; quantised rows and indices stay on the device for the decoder"}
         if split is None:
-            q_host = torch.empty_like(z_host)
+            q_host = torch.empty(z_host.shape, dtype=z_host.dtype).pin_memory()
             i_host = torch.empty(N, dtype=torch.int64).pin_memory()
 
             def step_e2e_full():
@@ -447,19 +447,26 @@ def fp32_tier(ctx, key, mod, z, iters=5):
     dev = ctx.dev
     zf = z.float()
     E = mod.codebook.detach()
-    Eb = torch.empty((K, D), dtype=torch.bfloat16, device=dev)
     nrm = torch.empty(ops.norm_elems(K), dtype=torch.float32, device=dev)
     out = {}
     try:
+        Eb = ops.new_shadow(K, D, "fp32", dev)
         ops.prepare_codebook(E, "fp32", Eb, nrm)
-        ws = torch.zeros(ops.workspace_bytes(N, K, D, zf.dtype), dtype=torch.uint8, device=dev)
+        ws = torch.zeros(ops.workspace_bytes(N, K, D, zf.dtype, "fp32"), dtype=torch.uint8, device=dev)
         idx = torch.empty(N, dtype=torch.int32, device=dev)
+        idx2 = torch.empty(N, dtype=torch.int32, device=dev)
         fn = lambda: ops.assign(zf, E, Eb, nrm, "fp32", idx, None, ws, presort=True, ws_clean=True)
         fn(); torch.cuda.synchronize()
         t = time_kernel(fn, iters, ctx.flush)
+        fn2 = lambda: ops.assign(zf, E, None, nrm, "fp32_simt", idx2, None, ws, presort=True, ws_clean=True)
+        fn2(); torch.cuda.synchronize()
+        t2 = time_kernel(fn2, 2, ctx.flush)
         tf = 2.0 * N * K * D / (t * 1e-3) / 1e12
         out = {"ms_per_launch": t, "algorithmic_tflops": tf, "latents": "fp32",
-               "note": "search='fp32' (1e-5 tier) timed alone, 2*N*K*D algorithmic flops"}
+               "kernel": "split_bf16 staging + assign_tc_kernel, split operands (z = hi + lo, E = hi + lo, 3 bf16 MMAs per "
+                         "product, fp32 accumulate in TMEM)",
+               "cuda_core_kernel_ms": t2, "index_disagreements_vs_cuda_core_kernel": int((idx != idx2).sum()),
+               "note": "search='fp32' (1e-5 tier) timed alone incl. the staging pass, 2*N*K*D algorithmic flops"}
     except Exception as exc:                       # never fail the headline because of the side record
         out = {"error": str(exc)[:300]}
     return out

@@ -35,14 +35,22 @@ extern "C" {
 typedef struct CUstream_st* vq_stream_t; /* == cudaStream_t */
 #endif
 
-#define VQ_ABI_VERSION 2
+#define VQ_ABI_VERSION 3
 
 enum { VQ_OK = 0, VQ_ERR_ARG = 1, VQ_ERR_CUDA = 2, VQ_ERR_UNSUPPORTED = 3 };
-enum { VQ_DT_BF16 = 0, VQ_DT_F32 = 1 };
+/* storage type of latents and quantised rows.  fp16 is the reference script's DEFAULT autocast dtype
+ * (scripts/train_vqvae.py:284-286); bf16 with --bf16, fp32 with --no_amp. */
+enum { VQ_DT_BF16 = 0, VQ_DT_F32 = 1, VQ_DT_F16 = 2 };
 /* arithmetic of the distance search */
 enum {
-    VQ_SEARCH_BF16 = 0, /* z, E rounded to bf16, fp32 accumulate: tcgen05 tensor-core kernel            */
-    VQ_SEARCH_F32 = 1,  /* fp32 FMA on the CUDA cores, the 1e-5 tier                                     */
+    VQ_SEARCH_BF16 = 0, /* z, E rounded to bf16, fp32 accumulate: tcgen05 tensor-core kernel (bf16 latents native;
+                           fp32 / fp16 latents are staged as bf16 in ws)                                   */
+    VQ_SEARCH_F32 = 1,  /* the 1e-5 tier: fp32 products.  On the tensor cores as a split-operand search (z and E each
+                           as hi + lo bf16 pieces, three MMAs per product, fp32 accumulate in TMEM) when the caller
+                           passes the split shadow and D % 8 == 0, D <= 256; fp32 FMA on the CUDA cores otherwise   */
+    VQ_SEARCH_F16 = 2,  /* fp16 latents x fp16-rounded codebook, fp32 accumulate: the same tcgen05 kernel with fp16
+                           operands -- no staging, no cast (in_dtype must be VQ_DT_F16)                     */
+    VQ_SEARCH_SIMT = 1024, /* flag, with VQ_SEARCH_F32: force the CUDA-core kernel (comparison / tests)     */
     VQ_SEARCH_PRESORT = 256, /* flag, OR-ed in (vq_assign only, needs ws): the search also leaves in ws the per-code
                                histogram of idx, each row's rank inside its code and the exclusive scan, so that
                                vq_gather_st_loss_scatter(... | VQ_STAT_PRESORTED) can skip its own histogram passes */
@@ -69,12 +77,18 @@ const char* vq_last_error(void);
  * (padding = +inf) followed by K_pad * 8 floats of search-private data (-||e||^2/2 as a tensor-core operand image). */
 int vq_norm_elems(int K);
 
-/* Scratch bytes for one step at these sizes (covers vq_assign and vq_gather_st_loss_scatter). */
-int vq_workspace_bytes(int64_t N, int K, int D, int in_dtype, size_t* out_bytes /* host */);
+/* Scratch bytes for one step at these sizes and this search kind (covers vq_assign and vq_gather_st_loss_scatter;
+ * the staging region the search kind needs comes last, everything else sits at the same offsets for every kind). */
+int vq_workspace_bytes(int64_t N, int K, int D, int in_dtype, int search, size_t* out_bytes /* host */);
 
-/* a-7 tail: refresh what the search reads.  E_bf16 [K, D] bf16 shadow (may be NULL for VQ_SEARCH_F32);
- * e_norm2 [vq_norm_elems(K)] fp32 = ||e_k||^2 of the bf16-rounded rows (VQ_SEARCH_BF16) or of the fp32
- * rows (VQ_SEARCH_F32); padding entries are +inf. */
+/* Number of 16-bit elements the search shadow ("E_bf16" below) must hold for this search kind: K * D (bf16 rows for
+ * VQ_SEARCH_BF16, fp16 rows for VQ_SEARCH_F16) or, for VQ_SEARCH_F32, 2 * K_pad * D: the hi and lo bf16 planes of the
+ * split tensor-core tier (K_pad = K rounded up to 256; pad rows zero).  16-byte aligned. */
+int64_t vq_shadow_elems(int K, int D, int search);
+
+/* a-7 tail: refresh what the search reads.  E_bf16: the 16-bit shadow of vq_shadow_elems(K, D, search) elements (for
+ * VQ_SEARCH_F32 it may be NULL: the search then runs on the CUDA cores); e_norm2 [vq_norm_elems(K)] fp32 = ||e_k||^2
+ * of the rounded rows (VQ_SEARCH_BF16 / VQ_SEARCH_F16) or of the fp32 rows (VQ_SEARCH_F32); padding entries are +inf. */
 int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf16, float* e_norm2,
                         vq_stream_t stream);
 
@@ -145,7 +159,7 @@ int vq_backward(const void* z, const void* q, const void* grad_q /* nullable */,
 int vq_codebook_grad(const float* resid_sum, int K, int D, const float* grad_loss /* device [1] */, float coef,
                      float* grad_E, vq_stream_t stream);
 
-/* fp32 -> bf16 row cast used when fp32 latents go through VQ_SEARCH_BF16 (dst is [N, D] dense). */
+/* fp32 -> bf16 row cast (what vq_assign does internally when fp32 latents go through VQ_SEARCH_BF16; dst [N, D] dense). */
 int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_stream_t stream);
 
 /* a-0 layout ingest: batched transpose src [B, R, C] -> dst [B, C, R] (dense, dtype VQ_DT_*).  Channel-first latents

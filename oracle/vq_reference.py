@@ -55,20 +55,28 @@ def round_bf16(x: torch.Tensor) -> torch.Tensor:
     return x.to(torch.bfloat16).to(torch.float32)
 
 
+def round_f16(x: torch.Tensor) -> torch.Tensor:
+    return x.to(torch.float16).to(torch.float32)
+
+
+def round_to(x: torch.Tensor, precision: str) -> torch.Tensor:
+    """What the 16-bit tensor-core searches see: the operand rounded to the search's element type."""
+    return round_bf16(x) if precision == "bf16" else round_f16(x) if precision == "fp16" else x
+
+
 def code_norms(E: torch.Tensor, precision: str) -> torch.Tensor:
-    """||e_k||^2 in fp32.  bf16 mode: of the bf16-rounded codebook, so that the search is
+    """||e_k||^2 in fp32.  bf16 / fp16 mode: of the rounded codebook, so that the search is
     the exact nearest neighbour among the rounded vectors (CHOICE)."""
-    Ef = E.detach().to(torch.float32)
-    if precision == "bf16":
-        Ef = round_bf16(Ef)
+    Ef = round_to(E.detach().to(torch.float32), precision)
     return (Ef * Ef).sum(dim=1)
 
 
 def scores(z: torch.Tensor, E: torch.Tensor, precision: str = "fp32") -> torch.Tensor:
     """s[n,k] = ||e_k||^2 - 2 z_n.e_k   ( = d[n,k] - ||z_n||^2, same argmin ).
 
-    precision "fp32": everything fp32.  "bf16": z and E rounded to bf16, products
-    accumulated in fp32 (what a bf16 tensor-core GEMM with fp32 accumulate computes).
+    precision "fp32": everything fp32.  "bf16" / "fp16": z and E rounded to that type, products
+    accumulated in fp32 (what a 16-bit tensor-core GEMM with fp32 accumulate computes; fp16 is
+    the reference script's default autocast dtype, scripts/train_vqvae.py:284-286).
     "fp64": for near-tie adjudication in tests.
     """
     if precision == "fp64":
@@ -76,8 +84,8 @@ def scores(z: torch.Tensor, E: torch.Tensor, precision: str = "fp32") -> torch.T
         return (Ef * Ef).sum(1)[None, :] - 2.0 * (zf @ Ef.t())
     zf = z.detach().to(torch.float32)
     Ef = E.detach().to(torch.float32)
-    if precision == "bf16":
-        zf, Ef = round_bf16(zf), round_bf16(Ef)
+    if precision in ("bf16", "fp16"):
+        zf, Ef = round_to(zf, precision), round_to(Ef, precision)
     elif precision != "fp32":
         raise ValueError(precision)
     return code_norms(E, precision)[None, :] - 2.0 * (zf @ Ef.t())
@@ -104,9 +112,7 @@ def assign(z: torch.Tensor, E: torch.Tensor, precision: str = "fp32",
         smin, i = torch.min(s, dim=1)          # first minimal index
         # torch.min(dim) documents no tie order; argmin does. Use argmin for the index.
         i = torch.argmin(s, dim=1)
-        zf = zc.detach().to(torch.float32)
-        if precision == "bf16":
-            zf = round_bf16(zf)
+        zf = round_to(zc.detach().to(torch.float32), precision)
         z2 = (zf * zf).sum(1)
         ok = row_is_finite(zc)
         idx[a:a + chunk] = torch.where(ok, i, torch.zeros_like(i))
@@ -295,10 +301,8 @@ def near_tie_report(z: torch.Tensor, E: torch.Tensor, idx_test: torch.Tensor, id
     out = {"n": int(z.shape[0]), "mismatch": int(bad.numel()), "near_tie": 0, "hard": 0, "max_rel_gap": 0.0}
     if bad.numel() == 0:
         return out
-    zf = z[bad].detach().float()
-    Ef = E.detach().float()
-    if precision == "bf16":
-        zf, Ef = round_bf16(zf), round_bf16(Ef)
+    zf = round_to(z[bad].detach().float(), precision)
+    Ef = round_to(E.detach().float(), precision)
     zd, Ed = zf.double(), Ef.double()
     dt = ((zd - Ed[idx_test[bad]]) ** 2).sum(1)
     dr = ((zd - Ed[idx_ref[bad]]) ** 2).sum(1)

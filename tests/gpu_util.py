@@ -14,10 +14,10 @@ def cuda_step(z_cpu, E_cpu, search, dtype=torch.float32, deterministic=False, st
     E = E_cpu.to(dev).float().contiguous()
     N, D = z.shape
     K = E.shape[0]
-    E_bf16 = torch.empty((K, D), dtype=torch.bfloat16, device=dev)
+    E_bf16 = ops.new_shadow(K, D, search, dev)       # bf16 rows / fp16 rows / hi + lo planes of the split fp32 tier
     norms = torch.empty(ops.norm_elems(K), dtype=torch.float32, device=dev)
     ops.prepare_codebook(E, search, E_bf16, norms)
-    ws = torch.empty(ops.workspace_bytes(N, K, D, dtype), dtype=torch.uint8, device=dev)
+    ws = torch.empty(ops.workspace_bytes(N, K, D, dtype, search), dtype=torch.uint8, device=dev)
     idx = torch.full((N,), -1, dtype=torch.int32, device=dev)
     smin = torch.empty(N, dtype=torch.float32, device=dev) if want_smin else None
     # (1) stand-alone calls: the pass builds its own counting sort
@@ -71,7 +71,7 @@ def cuda_step(z_cpu, E_cpu, search, dtype=torch.float32, deterministic=False, st
             scale = sums[fin].abs().max().clamp_min(1e-30) if bool(fin.any()) else 1.0
             assert float(((sums3 - sums)[fin].abs().max() if bool(fin.any()) else 0.0) / scale) <= 1e-5
     out = dict(idx=idx.cpu().long(), raw_idx=raw_idx.cpu().long(), q=q.cpu(), sqerr=sq.cpu()[0],
-               norms=norms.cpu(), E_bf16=E_bf16.cpu())
+               norms=norms.cpu(), E_bf16=E_bf16.cpu()[:K * D].view(K, D))
     if want_smin:
         out["smin"] = smin.cpu()
     if stats:
@@ -82,9 +82,9 @@ def cuda_step(z_cpu, E_cpu, search, dtype=torch.float32, deterministic=False, st
 def check_step_against_oracle(z_cpu, E_cpu, search, dtype=torch.float32, rel=1e-5, tol=None, **kw):
     """Full single-step parity vs the oracle.  Index rule (north_star): bit-exact except near-ties
     (|delta d| < 1e-5 relative), which are counted and returned."""
-    prec = "bf16" if search == "bf16" else "fp32"
+    prec = search if search in ("bf16", "fp16") else "fp32"     # "fp32" (split tensor-core tier) and "fp32_simt": fp32 oracle
     if tol is None:
-        tol = 1e-3 if dtype == torch.bfloat16 else 1e-5          # north_star tolerances
+        tol = 1e-3 if dtype in (torch.bfloat16, torch.float16) else 1e-5          # north_star tolerances
     zin = z_cpu.to(dtype)                                        # what the kernel actually receives
     out = cuda_step(z_cpu, E_cpu, search, dtype, **kw)
     ref_idx, ref_dmin = R.assign(zin.float(), E_cpu, prec)

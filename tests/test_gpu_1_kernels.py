@@ -128,7 +128,7 @@ def test_ema_update_kernel_vs_oracle():
     dE, dn, dm = E.to(dev), n0.to(dev), m0.to(dev)
     du, ds = u0.to(dev), s0.to(dev)
     ppl = torch.zeros(1, device=dev); ndead = torch.zeros(1, dtype=torch.int32, device=dev)
-    Eb = torch.empty((K, D), dtype=torch.bfloat16, device=dev)
+    Eb = ops.new_shadow(K, D, "bf16", dev)
     nrm = torch.empty(ops.norm_elems(K), device=dev)
     ws = torch.empty(ops.workspace_bytes(16, K, D, torch.float32), dtype=torch.uint8, device=dev)
     ops.ema_update(dE, dn, dm, cnt.to(dev), sums.to(dev), 0.97, 1e-5, True, "bf16", Eb, nrm, du, ds, ppl, ndead, 3,
@@ -139,7 +139,7 @@ def test_ema_update_kernel_vs_oracle():
     np.testing.assert_allclose(dm.cpu().numpy(), m1.numpy(), rtol=1e-6, atol=1e-7)
     assert torch.equal(du.cpu(), u1) and torch.equal(ds.cpu(), s1) and int(ndead) == nd
     np.testing.assert_allclose(float(ppl), float(R.perplexity(cnt)), rtol=1e-5)
-    assert torch.equal(Eb.cpu(), dE.cpu().to(torch.bfloat16))
+    assert torch.equal(Eb.cpu().view(K, D), dE.cpu().to(torch.bfloat16))
     np.testing.assert_allclose(nrm.cpu()[:K].numpy(), R.code_norms(dE.cpu(), "bf16").numpy(), rtol=1e-5)
     Kp = (K + 255) // 256 * 256                      # norms are padded to the 256-code search tile with +inf
     assert torch.isinf(nrm.cpu()[K:Kp]).all()

@@ -83,7 +83,7 @@ def test_tc_unsupported_shape_is_loud():
     dev = torch.device("cuda:0")
     z = torch.randn(10, 12, device=dev).to(torch.bfloat16)       # D % 8 != 0
     E = torch.randn(4, 12, device=dev)
-    Eb = torch.empty((4, 12), dtype=torch.bfloat16, device=dev)
+    Eb = ops.new_shadow(4, 12, "bf16", dev)
     nrm = torch.empty(ops.norm_elems(4), device=dev)
     ops.prepare_codebook(E, "bf16", Eb, nrm)
     with pytest.raises(VQLibError, match="not supported"):
@@ -198,9 +198,8 @@ def test_reference_default_sizes_bf16(K, D):
 @pytest.mark.gpu
 @pytest.mark.parametrize("search", ["auto", "fp32"])
 def test_fp16_autocast_input(search):
-    """scripts/train_vqvae.py:284-286 runs the model under fp16 autocast unless --bf16.  Half latents are widened to
-    fp32 for gather / loss / statistics; "auto" sends them through the tensor-core search (staged as bf16),
-    search="fp32" keeps the exact tier."""
+    """scripts/train_vqvae.py:284-286 runs the model under fp16 autocast unless --bf16.  fp16 rows go to the kernels as
+    they are: "auto" = tensor-core search on fp16 operands (fp16-rounded codebook), search="fp32" keeps the exact tier."""
     from vqvae_b200 import VectorQuantizer
     torch.manual_seed(5)
     mod = VectorQuantizer(32, 64, quantizer="st", search=search).cuda()
@@ -211,13 +210,10 @@ def test_fp16_autocast_input(search):
         q, loss, idx = mod(z)
     assert q.dtype == torch.float16 and loss.dtype == torch.float32 and idx.shape == (4, 1000)
     zf, E = z.detach().float().cpu().reshape(-1, 32), mod.codebook.detach().cpu()
-    if search == "fp32":
-        ref_idx, _ = R.assign(zf, E, "fp32")
-        assert torch.equal(idx.cpu().reshape(-1), ref_idx)
-    else:
-        ref_idx, _ = R.assign(zf, E, "bf16")
-        rep = R.near_tie_report(zf, E, idx.cpu().reshape(-1), ref_idx, precision="bf16")
-        assert rep["hard"] == 0, rep
+    prec = "fp32" if search == "fp32" else "fp16"
+    ref_idx, _ = R.assign(zf, E, prec)
+    rep = R.near_tie_report(zf, E, idx.cpu().reshape(-1), ref_idx, precision=prec)
+    assert rep["hard"] == 0, rep
     assert torch.equal(q.detach().float().cpu().reshape(-1, 32), E[idx.cpu().reshape(-1)].to(torch.float16).float())
     mse = float(((zf - E[idx.cpu().reshape(-1)]) ** 2).mean())
     np.testing.assert_allclose(float(loss), 1.25 * mse, rtol=1e-4)          # loss on the exact fp32 values

@@ -27,20 +27,26 @@ def _lockstep(mod, ref, batches, tol, D):
             np.testing.assert_allclose(mod.codebook.detach().cpu().numpy(), ref.codebook.detach().numpy(), rtol=tol,
                                        atol=1e-6)
             assert torch.equal(mod.usage_total.cpu(), ref.usage_total)
+        else:
+            # the flipped rows sit in different codes from here on: put the oracle on the module's state so that the
+            # following steps are compared from a common starting point again (all flips were near-ties, checked above)
+            ref.load_state_dict({k: v.detach().cpu() for k, v in mod.state_dict().items()}, strict=False)
 
 
 @pytest.mark.parametrize("search,dtype,D,deterministic", [
     ("bf16", torch.bfloat16, 64, False),      # tensor-core search, vector pass: the production pairing
     ("bf16", torch.float32, 64, False),       # fp32 latents staged as bf16 (staging region sits behind the counters)
-    ("fp32", torch.float32, 32, False),       # CUDA-core search leaves the same by-product
+    ("fp32", torch.float32, 32, False),       # split tensor-core fp32 tier: two staged planes behind the counters
+    ("fp32_simt", torch.float32, 32, False),  # CUDA-core search leaves the same by-product
     ("fp32", torch.float32, 20, False),       # D % 4 != 0 for the 16-byte path: generic pass ignores the by-product
+    ("fp16", torch.float16, 64, False),       # native fp16 rows
     ("bf16", torch.bfloat16, 64, True),       # deterministic pass builds its own stable sort, must re-zero the counters
 ])
 def test_one_workspace_across_changing_batches(search, dtype, D, deterministic):
     from vqvae_b200 import VectorQuantizer
     torch.manual_seed(3)
     K = 96
-    prec = "bf16" if search == "bf16" else "fp32"
+    prec = search if search in ("bf16", "fp16") else "fp32"
     ref = R.VectorQuantizerOracle(D, K, beta=0.25, quantizer="ema", ema_decay=0.9, precision=prec)
     mod = VectorQuantizer(D, K, beta=0.25, quantizer="ema", ema_decay=0.9, search=search, deterministic=deterministic,
                           cuda_graph=False)
@@ -49,7 +55,7 @@ def test_one_workspace_across_changing_batches(search, dtype, D, deterministic):
     g = torch.Generator().manual_seed(11)
     sizes = [3000, 257, 40000, 1, 3000, 40000, 129]       # grows (new zero-filled workspace) and shrinks (same workspace)
     batches = [torch.randn(n, D, generator=g).to(dtype) for n in sizes]
-    _lockstep(mod, ref, batches, 1e-3 if prec == "bf16" or dtype == torch.bfloat16 else 1e-5, D)
+    _lockstep(mod, ref, batches, 1e-3 if prec != "fp32" or dtype != torch.float32 else 1e-5, D)
 
 
 def test_alternating_modes_share_the_workspace():

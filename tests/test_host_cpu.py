@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/vq_b200.h but not exported"
     assert set(names) == set(_lib.SIGNATURES), "ctypes binding and header disagree"
-    assert lib.vq_abi_version() == _lib.ABI_VERSION == 2
+    assert lib.vq_abi_version() == _lib.ABI_VERSION == 3
 
 
 def test_host_only_entry_points():
@@ -37,12 +37,19 @@ def test_host_only_entry_points():
     assert lib.vq_norm_elems(1) == 256 * 9 and lib.vq_norm_elems(256) == 256 * 9 and lib.vq_norm_elems(8192) == 8192 * 9
     assert lib.vq_norm_elems(1000) == 1024 * 9
     out = ctypes.c_size_t(0)
-    assert lib.vq_workspace_bytes(524288, 8192, 256, 0, ctypes.byref(out)) == 0
+    assert lib.vq_workspace_bytes(524288, 8192, 256, 0, 0, ctypes.byref(out)) == 0       # bf16 latents, bf16 search
     small = out.value
-    assert lib.vq_workspace_bytes(524288, 8192, 256, 1, ctypes.byref(out)) == 0
-    assert out.value >= small + 524288 * 256 * 2          # fp32 input needs the bf16 staging area
-    assert lib.vq_workspace_bytes(-1, 8192, 256, 0, ctypes.byref(out)) == 1   # VQ_ERR_ARG
+    assert lib.vq_workspace_bytes(524288, 8192, 256, 2, 2, ctypes.byref(out)) == 0       # fp16 latents, fp16 search: native
+    assert out.value == small
+    assert lib.vq_workspace_bytes(524288, 8192, 256, 1, 0, ctypes.byref(out)) == 0
+    assert out.value >= small + 524288 * 256 * 2          # fp32 latents under the bf16 search: one bf16 staging plane
+    assert lib.vq_workspace_bytes(524288, 8192, 256, 1, 1, ctypes.byref(out)) == 0
+    assert out.value >= small + 524288 * 256 * 4          # split fp32 tier: hi + lo planes
+    assert lib.vq_workspace_bytes(524288, 8192, 264, 1, 1, ctypes.byref(out)) == 0       # D > 256: CUDA-core kernel, no staging
+    assert lib.vq_workspace_bytes(-1, 8192, 256, 0, 0, ctypes.byref(out)) == 1   # VQ_ERR_ARG
     assert b"bad arguments" in lib.vq_last_error()
+    assert lib.vq_shadow_elems(1000, 128, 0) == 1000 * 128 and lib.vq_shadow_elems(1000, 128, 2) == 1000 * 128
+    assert lib.vq_shadow_elems(1000, 128, 1) == 2 * 1024 * 128
 
 
 def test_module_contract_on_cpu():

@@ -23,7 +23,7 @@ for name in sys.argv[1:] or ["c2", "c4"]:
     N, K, D = wl["N"], wl["K"], wl["D"]
     z, E = make_inputs(wl, 0, dev)
     E = E.to(dev)
-    Eb = torch.empty((K, D), dtype=torch.bfloat16, device=dev)
+    Eb = ops.new_shadow(K, D, "bf16", dev)
     nrm = torch.empty(ops.norm_elems(K), device=dev)
     ops.prepare_codebook(E, "bf16", Eb, nrm)
     ws = torch.empty(ops.workspace_bytes(N, K, D, z.dtype), dtype=torch.uint8, device=dev)

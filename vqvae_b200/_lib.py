@@ -13,14 +13,15 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("VQ_B200_LIB") or os.path.join(HERE, "libvq_b200.so")   # env: tuning variants only
 
 VQ_OK, VQ_ERR_ARG, VQ_ERR_CUDA, VQ_ERR_UNSUPPORTED = 0, 1, 2, 3
-VQ_DT_BF16, VQ_DT_F32 = 0, 1
-VQ_SEARCH_BF16, VQ_SEARCH_F32 = 0, 1
+VQ_DT_BF16, VQ_DT_F32, VQ_DT_F16 = 0, 1, 2
+VQ_SEARCH_BF16, VQ_SEARCH_F32, VQ_SEARCH_F16 = 0, 1, 2
+VQ_SEARCH_SIMT = 1024       # with VQ_SEARCH_F32: force the CUDA-core kernel
 VQ_STAT_SUM_Z, VQ_STAT_SUM_RESID = 0, 1
 VQ_STAT_ACCUMULATE = 16
 VQ_STAT_PRESORTED = 32      # idx comes from vq_assign(... | VQ_SEARCH_PRESORT) on the same workspace
 VQ_SEARCH_WS_CLEAN = 512    # caller vouches that the workspace counters are zero (see include/vq_b200.h)
 VQ_SEARCH_PRESORT = 256     # vq_assign also leaves histogram / ranks / scan of idx in the workspace
-ABI_VERSION = 2
+ABI_VERSION = 3
 MAX_PEERS, IPC_HANDLE_BYTES = 16, 64
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
@@ -33,7 +34,8 @@ SIGNATURES = {
     "vq_set_pdl_mask": (_i, [_i]),
     "vq_set_peer_timeout_ms": (_i64, [_i64]),
     "vq_norm_elems": (_i, [_i]),
-    "vq_workspace_bytes": (_i, [_i64, _i, _i, _i, C.POINTER(C.c_size_t)]),
+    "vq_workspace_bytes": (_i, [_i64, _i, _i, _i, _i, C.POINTER(C.c_size_t)]),
+    "vq_shadow_elems": (_i64, [_i, _i, _i]),
     "vq_prepare_codebook": (_i, [_p, _i, _i, _i, _p, _p, _p]),
     "vq_assign": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _p, _i, _i, _p, _p, _p, _p]),
     "vq_gather_st_loss_scatter": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _i, _p, _i, _i64, _p, _p, _p, _i, _i, _p, _p, _f,

@@ -92,18 +92,30 @@ int64_t vq_set_peer_timeout_ms(int64_t ms) {
 // K_pad fp32 norms followed by the K_pad x 32 B "aug" image (vq_ema.cu: write_aug)
 int vq_norm_elems(int K) { return K <= 0 ? 0 : round_up(K, 256) * 9; }
 
-int vq_workspace_bytes(int64_t N, int K, int D, int in_dtype, size_t* out_bytes) {
+static bool dtype_ok(int dt) { return dt == VQ_DT_BF16 || dt == VQ_DT_F32 || dt == VQ_DT_F16; }
+static bool search_ok(int s) { return s == VQ_SEARCH_BF16 || s == VQ_SEARCH_F32 || s == VQ_SEARCH_F16; }
+
+int vq_workspace_bytes(int64_t N, int K, int D, int in_dtype, int search, size_t* out_bytes) {
     VQ_REQUIRE(out_bytes != nullptr, "vq_workspace_bytes: out_bytes is NULL");
-    VQ_REQUIRE(N >= 0 && K > 0 && D > 0 && (in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32),
-               "vq_workspace_bytes: bad arguments N=%lld K=%d D=%d in_dtype=%d", (long long)N, K, D, in_dtype);
-    *out_bytes = ws_layout(N, K, D, in_dtype).total;
+    VQ_REQUIRE(N >= 0 && K > 0 && D > 0 && dtype_ok(in_dtype) && search_ok(search),
+               "vq_workspace_bytes: bad arguments N=%lld K=%d D=%d in_dtype=%d search=%d", (long long)N, K, D, in_dtype,
+               search);
+    *out_bytes = ws_layout(N, K, D, in_dtype, search).total;
     return VQ_OK;
+}
+
+// 16-bit elements the search shadow must hold: K * D rows of bf16 (VQ_SEARCH_BF16) or fp16 (VQ_SEARCH_F16); for
+// VQ_SEARCH_F32 the hi / lo bf16 planes of the split tensor-core tier, [2][K_pad][D], K_pad = K rounded up to 256
+int64_t vq_shadow_elems(int K, int D, int search) {
+    if (K <= 0 || D <= 0) return 0;
+    return search == VQ_SEARCH_F32 ? (int64_t)2 * round_up(K, 256) * D : (int64_t)K * D;
 }
 
 int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf16, float* e_norm2,
                         vq_stream_t stream) {
-    VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_prepare_codebook: bad search mode %d", search);
-    VQ_REQUIRE(search != VQ_SEARCH_BF16 || E_bf16 != nullptr, "vq_prepare_codebook: E_bf16 required for VQ_SEARCH_BF16");
+    VQ_REQUIRE(search_ok(search), "vq_prepare_codebook: bad search mode %d", search);
+    VQ_REQUIRE(search == VQ_SEARCH_F32 || E_bf16 != nullptr, "vq_prepare_codebook: the 16-bit shadow is required for "
+               "VQ_SEARCH_BF16 / VQ_SEARCH_F16");
     return launch_ema_update(const_cast<float*>(E_f32), nullptr, nullptr, nullptr, nullptr, K, D, 0.f, 0.f, 0, search,
                              E_bf16, e_norm2, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, stream, nullptr, nullptr,
                              0, 0, 0);
@@ -111,7 +123,7 @@ int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf
 
 int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32, const void* E_bf16,
               const float* e_norm2, int K, int search, int32_t* idx, float* smin, void* ws, vq_stream_t stream) {
-    VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_assign: bad in_dtype %d", in_dtype);
+    VQ_REQUIRE(dtype_ok(in_dtype), "vq_assign: bad in_dtype %d", in_dtype);
     VQ_REQUIRE(N >= 0 && D > 0 && K > 0 && ldz >= D, "vq_assign: bad shape N=%lld D=%d K=%d ldz=%lld", (long long)N, D,
                K, (long long)ldz);
     if (N == 0) return VQ_OK;
@@ -119,12 +131,14 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
     VQ_REQUIRE(z != nullptr, "vq_assign: z is NULL");
     Presort ps{nullptr, nullptr, nullptr, nullptr};
     const bool ws_clean = (search & VQ_SEARCH_WS_CLEAN) != 0;
-    search &= ~VQ_SEARCH_WS_CLEAN;
-    if (search & VQ_SEARCH_PRESORT) {
-        search &= ~VQ_SEARCH_PRESORT;
+    const bool want_presort = (search & VQ_SEARCH_PRESORT) != 0;
+    const bool force_simt = (search & VQ_SEARCH_SIMT) != 0;
+    search &= ~(VQ_SEARCH_WS_CLEAN | VQ_SEARCH_PRESORT | VQ_SEARCH_SIMT);
+    VQ_REQUIRE(search_ok(search), "vq_assign: bad search mode %d", search);
+    if (want_presort) {
         VQ_REQUIRE(ws != nullptr, "vq_assign: VQ_SEARCH_PRESORT needs the workspace");
         VQ_REQUIRE(N < (int64_t(1) << 31), "vq_assign: VQ_SEARCH_PRESORT needs N < 2^31");
-        const WsLayout L = ws_layout(N, K, D, in_dtype);
+        const WsLayout L = ws_layout(N, K, D, in_dtype, search);
         uint8_t* w = static_cast<uint8_t*>(ws);
         ps.hist = reinterpret_cast<int*>(w + L.cnt);
         ps.rank = reinterpret_cast<int*>(w + L.rank);
@@ -135,35 +149,48 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
         if (!ws_clean) VQ_CHECK_CUDA(cudaMemsetAsync(ps.hist, 0, (size_t)(2 * K + 2) * 4, stream));
     }
     if (search == VQ_SEARCH_F32) {
+        // the 1e-5 tier.  With the split shadow ([2][K_pad][D] hi / lo bf16 planes from vq_prepare_codebook /
+        // vq_ema_update) and a shape the tensor-core kernel takes: three bf16 MMAs per product on tcgen05; otherwise
+        // (odd D, D > 256, no shadow, VQ_SEARCH_SIMT) the fp32 FMA kernel, which has no shape limits
+        if (!force_simt && E_bf16 != nullptr && ws != nullptr && assign_tc_split_supported(N, D, K)) {
+            void* stage = static_cast<uint8_t*>(ws) + ws_layout(N, K, D, in_dtype, search).zbf16;
+            int rc = launch_split_bf16(z, in_dtype, N, D, ldz, stage, stream);
+            if (rc != VQ_OK) return rc;
+            return launch_assign_tc(stage, N, D, D, E_bf16, e_norm2, K, VQ_SEARCH_F32, idx, smin, ps, stream);
+        }
         VQ_REQUIRE(E_f32 != nullptr, "vq_assign: E_f32 required for VQ_SEARCH_F32");
         return launch_assign_simt(z, in_dtype, N, D, ldz, E_f32, e_norm2, K, idx, smin, ps, stream);
     }
-    VQ_REQUIRE(search == VQ_SEARCH_BF16, "vq_assign: bad search mode %d", search);
-    VQ_REQUIRE(E_bf16 != nullptr, "vq_assign: E_bf16 required for VQ_SEARCH_BF16");
+    VQ_REQUIRE(E_bf16 != nullptr, "vq_assign: the 16-bit codebook shadow is required for VQ_SEARCH_BF16 / VQ_SEARCH_F16");
     const void* zb = z;
     int64_t ldb = ldz;
-    if (in_dtype == VQ_DT_F32) {
-        VQ_REQUIRE(ws != nullptr, "vq_assign: workspace required to stage fp32 latents as bf16");
-        void* stage = static_cast<uint8_t*>(ws) + ws_layout(N, K, D, in_dtype).zbf16;
-        int rc = launch_cast_bf16(static_cast<const float*>(z), N, D, ldz, stage, stream);
+    if (search == VQ_SEARCH_F16) {
+        if (in_dtype != VQ_DT_F16) {
+            set_error("vq_assign(VQ_SEARCH_F16) takes fp16 latents; use VQ_SEARCH_BF16 or VQ_SEARCH_F32 for in_dtype %d", in_dtype);
+            return VQ_ERR_UNSUPPORTED;
+        }
+    } else if (in_dtype != VQ_DT_BF16) {             // fp32 / fp16 latents under the bf16 search: staged as bf16
+        VQ_REQUIRE(ws != nullptr, "vq_assign: workspace required to stage the latents as bf16");
+        void* stage = static_cast<uint8_t*>(ws) + ws_layout(N, K, D, in_dtype, search).zbf16;
+        int rc = launch_cast_bf16(z, in_dtype, N, D, ldz, stage, stream);
         if (rc != VQ_OK) return rc;
         zb = stage;
         ldb = D;
     }
     if (!assign_tc_supported(N, D, ldb, K)) {
-        set_error("vq_assign(VQ_SEARCH_BF16): shape N=%lld D=%d ld=%lld K=%d not supported by the tensor-core kernel "
+        set_error("vq_assign(tensor core): shape N=%lld D=%d ld=%lld K=%d not supported by the tensor-core kernel "
                   "(needs D %% 8 == 0, 8 <= D <= 512, ld %% 8 == 0); use VQ_SEARCH_F32",
                   (long long)N, D, (long long)ldb, K);
         return VQ_ERR_UNSUPPORTED;
     }
-    return launch_assign_tc(zb, N, D, ldb, E_bf16, e_norm2, K, idx, smin, ps, stream);
+    return launch_assign_tc(zb, N, D, ldb, E_bf16, e_norm2, K, search, idx, smin, ps, stream);
 }
 
 int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx,
                               const float* E_f32, int K, void* q_out, int out_dtype, int64_t ldq, float* sq_err_sum,
                               float* code_cnt, float* code_sum, int stat_kind, int deterministic,
                               int64_t* idx64_out, float* loss_out, float loss_scale, void* ws, vq_stream_t stream) {
-    VQ_REQUIRE(in_dtype == VQ_DT_BF16 || in_dtype == VQ_DT_F32, "vq_gather_st_loss_scatter: bad in_dtype %d", in_dtype);
+    VQ_REQUIRE(dtype_ok(in_dtype), "vq_gather_st_loss_scatter: bad in_dtype %d", in_dtype);
     VQ_REQUIRE(out_dtype == in_dtype, "vq_gather_st_loss_scatter: out_dtype must equal in_dtype");
     {
         const int base_kind = stat_kind & ~(VQ_STAT_ACCUMULATE | VQ_STAT_PRESORTED);
@@ -171,7 +198,7 @@ int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int
     }
     VQ_REQUIRE(E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (idx != nullptr && z != nullptr && q_out != nullptr)),
                "vq_gather_st_loss_scatter: NULL argument");
-    const PassExtra extra{idx64_out, loss_out, loss_scale};
+    const PassExtra extra{idx64_out, loss_out, loss_scale, 0};
     return launch_gather_pass(z, in_dtype, N, D, ldz, idx, E_f32, K, q_out, ldq, sq_err_sum, code_cnt, code_sum,
                               stat_kind, deterministic, extra, ws, stream);
 }
@@ -181,7 +208,7 @@ int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* cod
                   int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead, int dead_after,
                   int update_usage, void* ws, vq_stream_t stream) {
     VQ_REQUIRE(code_cnt != nullptr, "vq_ema_update: code_cnt is NULL");
-    VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_ema_update: bad search mode %d", search);
+    VQ_REQUIRE(search_ok(search), "vq_ema_update: bad search mode %d", search);
     return launch_ema_update(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, do_ema, search, E_bf16,
                              e_norm2, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws,
                              stream, nullptr, nullptr, 0, 0, 0);
@@ -193,7 +220,7 @@ int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D,
                      const void* const* peer_stats, void* const* peer_flags, int world, int rank, int epoch,
                      vq_stream_t stream) {
     VQ_REQUIRE(peer_stats != nullptr && peer_flags != nullptr, "vq_ema_update_dp: peer arrays are NULL");
-    VQ_REQUIRE(search == VQ_SEARCH_BF16 || search == VQ_SEARCH_F32, "vq_ema_update_dp: bad search mode %d", search);
+    VQ_REQUIRE(search_ok(search), "vq_ema_update_dp: bad search mode %d", search);
     return launch_ema_update(E_f32, ema_cnt, ema_sum, nullptr, nullptr, K, D, decay, eps, do_ema, search, E_bf16, e_norm2,
                              usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws, stream,
                              peer_stats, peer_flags, world, rank, epoch);
@@ -249,7 +276,7 @@ int vq_ipc_close(void* dev_ptr) {
 
 int vq_backward(const void* z, const void* q, const void* grad_q, int64_t N, int D, int64_t ldz,
                 const float* grad_loss, float coef, void* grad_z, int dtype, vq_stream_t stream) {
-    VQ_REQUIRE(dtype == VQ_DT_BF16 || dtype == VQ_DT_F32, "vq_backward: bad dtype %d", dtype);
+    VQ_REQUIRE(dtype_ok(dtype), "vq_backward: bad dtype %d", dtype);
     VQ_REQUIRE(N == 0 || (z != nullptr && q != nullptr && grad_z != nullptr && grad_loss != nullptr),
                "vq_backward: NULL argument");
     return launch_backward(z, q, grad_q, N, D, ldz, grad_loss, coef, grad_z, dtype, stream);
@@ -263,11 +290,11 @@ int vq_codebook_grad(const float* resid_sum, int K, int D, const float* grad_los
 
 int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_stream_t stream) {
     VQ_REQUIRE(N == 0 || (src != nullptr && dst != nullptr), "vq_cast_bf16: NULL argument");
-    return launch_cast_bf16(src, N, D, ld, dst, stream);
+    return launch_cast_bf16(src, VQ_DT_F32, N, D, ld, dst, stream);
 }
 
 int vq_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, vq_stream_t stream) {
-    VQ_REQUIRE(dtype == VQ_DT_BF16 || dtype == VQ_DT_F32, "vq_layout_transpose: bad dtype %d", dtype);
+    VQ_REQUIRE(dtype_ok(dtype), "vq_layout_transpose: bad dtype %d", dtype);
     VQ_REQUIRE((B == 0 || R == 0 || C == 0) || (src != nullptr && dst != nullptr), "vq_layout_transpose: NULL argument");
     return launch_layout_transpose(src, dst, B, R, C, dtype, stream);
 }

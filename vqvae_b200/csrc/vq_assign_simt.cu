@@ -3,6 +3,7 @@
 // fp32 or bf16 latents, fp32 master codebook.  Classic 64x64 register-tiled SGEMM shape with the score
 // tile folded into a per-row running argmin, so the N x K matrix is never stored either.
 // Definition: SURVEY.md 8(a-1); required by scripts/train_vqvae.py:11,287.
+#include <cuda_fp16.h>
 #include <math_constants.h>
 
 #include "vq_common.cuh"
@@ -20,6 +21,9 @@ template <>
 __device__ __forceinline__ float load_as_float<__nv_bfloat16>(const __nv_bfloat16* p) {
     return __bfloat162float(*p);
 }
+
+template <>
+__device__ __forceinline__ float load_as_float<__half>(const __half* p) { return __half2float(*p); }
 
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -102,13 +106,14 @@ assign_simt_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, const
     if (ps.hist != nullptr) presort_finish(ps, K, scan_sh);
 }
 
-__global__ void cast_bf16_kernel(const float* __restrict__ src, int64_t N, int D, int64_t ld,
+template <typename T>
+__global__ void cast_bf16_kernel(const T* __restrict__ src, int64_t N, int D, int64_t ld,
                                  __nv_bfloat16* __restrict__ dst) {
     const int64_t total = N * (int64_t)D;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = i / D;
         const int c = (int)(i - r * D);
-        dst[i] = __float2bfloat16_rn(src[r * ld + c]);
+        dst[i] = __float2bfloat16_rn(load_as_float<T>(src + r * ld + c));
     }
 }
 
@@ -119,7 +124,54 @@ __global__ void cast_bf16_vec_kernel(const float4* __restrict__ src, int64_t n4,
     }
 }
 
+// Split fp32 tier of the tensor-core search: x = hi + lo with hi = bf16(x), lo = bf16(x - hi) (16 significant bits; the
+// subtraction is exact in fp32), written as two dense [N, D] bf16 planes, plane 1 behind plane 0.
+template <typename T>
+__global__ void split_bf16_kernel(const T* __restrict__ src, int64_t N, int D, int64_t ld,
+                                  __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+    const int64_t total = N * (int64_t)D;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / D;
+        const int c = (int)(i - r * D);
+        const float x = load_as_float<T>(src + r * ld + c);
+        const __nv_bfloat16 h = __float2bfloat16_rn(x);
+        hi[i] = h;
+        lo[i] = __float2bfloat16_rn(x - __bfloat162float(h));
+    }
+}
+__global__ void split_bf16_vec_kernel(const float4* __restrict__ src, int64_t n4, uint2* __restrict__ hi,
+                                      uint2* __restrict__ lo) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldcs(src + i);
+        const uint2 h = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+        hi[i] = h;
+        lo[i] = make_uint2(pack_bf16(v.x - bf16_lo(h.x), v.y - bf16_hi(h.x)), pack_bf16(v.z - bf16_lo(h.y), v.w - bf16_hi(h.y)));
+    }
+}
+
 }  // namespace
+
+int launch_split_bf16(const void* src, int in_dtype, int64_t N, int D, int64_t ld, void* dst_planes, cudaStream_t st) {
+    VQ_REQUIRE(N >= 0 && D > 0 && ld >= D, "vq_assign(split): bad shape");
+    if (N == 0) return VQ_OK;
+    const int64_t total = N * (int64_t)D;
+    __nv_bfloat16* hi = static_cast<__nv_bfloat16*>(dst_planes);
+    __nv_bfloat16* lo = hi + total;
+    const int blocks = sm_count() * 8;
+    if (in_dtype == VQ_DT_F32 && ld == D && total % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 &&
+        (reinterpret_cast<uintptr_t>(dst_planes) & 7) == 0 && (total * 2) % 8 == 0)
+        split_bf16_vec_kernel<<<blocks, 256, 0, st>>>(static_cast<const float4*>(src), total / 4,
+                                                      reinterpret_cast<uint2*>(hi), reinterpret_cast<uint2*>(lo));
+    else if (in_dtype == VQ_DT_F32)
+        split_bf16_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(src), N, D, ld, hi, lo);
+    else if (in_dtype == VQ_DT_F16)
+        split_bf16_kernel<__half><<<blocks, 256, 0, st>>>(static_cast<const __half*>(src), N, D, ld, hi, lo);
+    else
+        split_bf16_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(src), N, D, ld, hi, lo);
+    VQ_CHECK_CUDA(cudaGetLastError());
+    count_launch();
+    return VQ_OK;
+}
 
 int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32,
                        const float* e_norm2, int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st) {
@@ -130,6 +182,9 @@ int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     if (in_dtype == VQ_DT_F32)
         assign_simt_kernel<float><<<(unsigned)grid, 256, 0, st>>>(static_cast<const float*>(z), N, D, ldz, E_f32,
                                                                   e_norm2, K, idx, smin, ps);
+    else if (in_dtype == VQ_DT_F16)
+        assign_simt_kernel<__half><<<(unsigned)grid, 256, 0, st>>>(static_cast<const __half*>(z), N, D, ldz, E_f32,
+                                                                   e_norm2, K, idx, smin, ps);
     else
         assign_simt_kernel<__nv_bfloat16><<<(unsigned)grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(z), N, D,
                                                                           ldz, E_f32, e_norm2, K, idx, smin, ps);
@@ -138,17 +193,22 @@ int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     return VQ_OK;
 }
 
-int launch_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, cudaStream_t st) {
+int launch_cast_bf16(const void* src, int in_dtype, int64_t N, int D, int64_t ld, void* dst, cudaStream_t st) {
     VQ_REQUIRE(N >= 0 && D > 0 && ld >= D, "vq_cast_bf16: bad shape");
+    VQ_REQUIRE(in_dtype == VQ_DT_F32 || in_dtype == VQ_DT_F16, "vq_cast_bf16: source must be fp32 or fp16");
     if (N == 0) return VQ_OK;
     const int64_t total = N * (int64_t)D;
     const int blocks = sm_count() * 8;
-    if (ld == D && total % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 &&
+    if (in_dtype == VQ_DT_F16)
+        cast_bf16_kernel<__half><<<blocks, 256, 0, st>>>(static_cast<const __half*>(src), N, D, ld,
+                                                         static_cast<__nv_bfloat16*>(dst));
+    else if (ld == D && total % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 &&
         (reinterpret_cast<uintptr_t>(dst) & 7) == 0)
         cast_bf16_vec_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const float4*>(src), total / 4,
                                                      static_cast<uint2*>(dst));
     else
-        cast_bf16_kernel<<<blocks, 256, 0, st>>>(src, N, D, ld, static_cast<__nv_bfloat16*>(dst));
+        cast_bf16_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(src), N, D, ld,
+                                                        static_cast<__nv_bfloat16*>(dst));
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();
     return VQ_OK;

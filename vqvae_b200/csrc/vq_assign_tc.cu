@@ -20,6 +20,12 @@
 //   warps 4..   epilogue (8 warps in pairs, 16 on single CTAs): warp w reads TMEM lanes 32*(w%4)..+31 (one row per
 //               thread) and one column part of each tile; the parts are merged through shared memory per slab.
 //
+// Operand kinds (all tcgen05 kind::f16, fp32 accumulate): bf16 latents x bf16 codebook shadow, fp16 latents x fp16 shadow
+// (the reference script's default autocast dtype, scripts/train_vqvae.py:284-286 -- no staging pass, no cast), and the
+// SPLIT form of the fp32 (1e-5) tier: z = z_hi + z_lo, e = e_hi + e_lo (bf16 pieces, 16 significant bits each), and
+// z.e ~ z_hi.e_hi + z_lo.e_hi + z_hi.e_lo accumulated in ONE TMEM accumulator -- three MMAs per product, the dropped
+// terms are below 2^-16 |z||e|.  The slab then holds two planes of z and the ring alternates e_hi / e_lo stages.
+//
 // Required by: scripts/train_vqvae.py:11,287 (VectorQuantizer inside model(batch));
 //              frl/config/frl_model_v0.yaml:29-33 (kind: vq, K, D).  Definition: SURVEY.md 8(a-1).
 #include <math_constants.h>
@@ -42,6 +48,16 @@ constexpr int MAX_EPI_PARTS = 4;   // epilogue warps = 4 TMEM lane quarters x co
 constexpr int TMEM_COLS = 512;
 constexpr int SMEM_LIMIT = 232448;  // 227 KiB opt-in maximum per CTA
 constexpr int NORM_SMEM_MAX = 8192; // codes whose ||e||^2 may be staged in shared memory (32 KiB)
+
+// What the MMAs multiply (host-chosen, see launch_assign_tc): instruction descriptor with the operand formats, the
+// A-side partner row (c1, c2, c3, 0, ...) of the mode-3 norm image as 16-bit patterns, and the split-plane geometry.
+struct OperandKind {
+    uint32_t idesc;          // kind::f16 instruction descriptor (bf16 or fp16 operands, fp32 accumulate, M, N)
+    uint32_t ones01, ones2;  // c1 | c2 << 16, c3: sum_i c_i * piece_i reproduces -||e||^2 / 2
+    int planes;              // 1, or 2 = split fp32 tier (hi / lo bf16 planes of z and of E)
+    int a_plane_rows;        // row offset of z's second plane in the staged [2][N][D] image
+    int b_plane_rows;        // row offset of E's second plane in the [2][K_pad][D] shadow
+};
 
 struct Ctl {
     uint64_t a_full[2], a_empty[2];
@@ -223,7 +239,7 @@ template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair>
 __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
                  const __grid_constant__ CUtensorMap tm_aug, const float* __restrict__ norms, int64_t N, int K, int D,
-                 int nkb, int nstages, int nabuf, int32_t* __restrict__ idx, float* __restrict__ smin,
+                 int nkb, int nstages, int nabuf, const OperandKind ok, int32_t* __restrict__ idx, float* __restrict__ smin,
 #ifdef VQ_TUNING
                  int dbg,               // 1..4: timing experiments of the tuning build (results are WRONG); 0 = off
 #endif
@@ -236,7 +252,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smA = smem;
-    uint8_t* smB = smA + nabuf * nkb * A_KB_BYTES;
+    uint8_t* smB = smA + nabuf * ok.planes * nkb * A_KB_BYTES;
     const int num_nb = (K + BN - 1) / BN;
     float* smN = reinterpret_cast<float*>(smB + nstages * B_ST);
     uint8_t* smP = reinterpret_cast<uint8_t*>(smN) + (kNormSmem ? num_nb * BN * 4 : 0);   // kMode 2: parked groups
@@ -252,7 +268,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     const int64_t nunits = kPair ? (gridDim.x >> 1) : gridDim.x;
     constexpr int SLAB = kPair ? 2 * BM : BM;                             // rows per slab of the unit
     const int64_t ntiles = (N + SLAB - 1) / SLAB;
-    const int a_bytes = nkb * A_KB_BYTES;
+    const int npl = ok.planes;                                            // 2: split fp32 tier
+    const int a_bytes = npl * nkb * A_KB_BYTES;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tm_z);
@@ -283,10 +300,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
         for (int i = threadIdx.x - 128; i < num_nb * (BN / 4); i += kEpiWarps * 32) dst[i] = __ldg(src + i);
     }
     if (kMode == 3 && threadIdx.x >= 128 && threadIdx.x < 256) {
-        // A-side partner of the aug image: every row is (1, 1, 1, 0, ..., 0), canonical no-swizzle K-major layout
+        // A-side partner of the aug image: every row is (c1, c2, c3, 0, ..., 0), canonical no-swizzle K-major layout
         const int r = threadIdx.x - 128;
         uint8_t* p = smO + (r >> 3) * 256 + (r & 7) * 16;
-        *reinterpret_cast<uint4*>(p) = make_uint4(0x3F803F80u, 0x00003F80u, 0u, 0u);
+        *reinterpret_cast<uint4*>(p) = make_uint4(ok.ones01, ok.ones2, 0u, 0u);
         *reinterpret_cast<uint4*>(p + 128) = make_uint4(0u, 0u, 0u, 0u);
         fence_proxy_async();               // generic-proxy writes -> visible to the tensor core's async proxy
     }
@@ -310,17 +327,16 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                 mbar_wait(&ctl->a_empty[buf], (use & 1u) ^ 1u, 1);
                 if (rank == 0) mbar_arrive_expect_tx(&ctl->a_full[buf], kPair ? 2 * a_bytes : a_bytes);
                 const int row0 = (int)(tile * SLAB + rank * BM);
-                for (int kb = 0; kb < nkb; ++kb) {
-                    if (kPair)
-                        tma_load_2d_hint_pair(smA + buf * a_bytes + kb * A_KB_BYTES, &tm_z, lead_a_full + 8u * buf, kb * BK, row0,
-                                              kEvictFirst);
-                    else
-                        tma_load_2d_hint(smA + buf * a_bytes + kb * A_KB_BYTES, &tm_z, &ctl->a_full[buf], kb * BK, row0,
-                                         kEvictFirst);
-                }
+                for (int pa = 0; pa < npl; ++pa)
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        uint8_t* dst = smA + buf * a_bytes + (pa * nkb + kb) * A_KB_BYTES;
+                        const int r = row0 + pa * ok.a_plane_rows;
+                        if (kPair) tma_load_2d_hint_pair(dst, &tm_z, lead_a_full + 8u * buf, kb * BK, r, kEvictFirst);
+                        else tma_load_2d_hint(dst, &tm_z, &ctl->a_full[buf], kb * BK, r, kEvictFirst);
+                    }
             };
             uint32_t st = 0, ph = 0, j = 0;
-            const int loads_per_slab = num_nb * (nkb + (kMode == 3 ? 1 : 0));
+            const int loads_per_slab = num_nb * (nkb * npl + (kMode == 3 ? 1 : 0));
             const int trigger = loads_per_slab < nstages ? loads_per_slab : nstages;
             if (nabuf == 2 && unit < ntiles) load_a(0, unit);
             for (int64_t tile = unit; tile < ntiles; tile += nunits, ++j) {
@@ -328,19 +344,21 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                 const int64_t next = tile + nunits;
                 int issued = 0;
                 for (int nb = 0; nb < num_nb; ++nb) {
-                    for (int kb = 0; kb < nkb; ++kb) {
+                    for (int kb = 0; kb < nkb; ++kb)
+                      for (int pb = 0; pb < npl; ++pb) {       // split tier: the e_hi stage, then the e_lo stage
                         mbar_wait(&ctl->b_empty[st], ph ^ 1, 2);
                         if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[st], B_ST_BYTES);   // 32 KiB per stage either way
+                        const int erow = nb * BN + pb * ok.b_plane_rows;
                         if (kPair)
                             tma_load_2d_hint_pair(smB + st * B_ST, &tm_e, lead_b_full + 8u * st, kb * BK,
-                                                  nb * BN + (int)rank * B_ROWS, kEvictLast);
+                                                  erow + (int)rank * B_ROWS, kEvictLast);
                         else
-                            tma_load_2d_hint(smB + st * B_ST, &tm_e, &ctl->b_full[st], kb * BK, nb * BN, kEvictLast);
+                            tma_load_2d_hint(smB + st * B_ST, &tm_e, &ctl->b_full[st], kb * BK, erow, kEvictLast);
                         if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                         // next slab's rows: requested once this slab's first ring-full of codebook stages is in
                         // flight, i.e. about when the previous slab retires and frees the other A buffer
                         if (++issued == trigger && nabuf == 2 && next < ntiles) load_a(j + 1, next);
-                    }
+                      }
                     if (kMode == 3) {       // one more ring stage per tile: the 8 KiB aug block of these 256 codes
                         mbar_wait(&ctl->b_empty[st], ph ^ 1, 2);
                         if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[st], 8192);
@@ -358,7 +376,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (pair: the leader CTA only)
         if (rank == 0 && elect_one()) {
-            constexpr uint32_t idesc = make_idesc_bf16(kPair ? 2 * BM : BM, BN);
+            const uint32_t idesc = ok.idesc;
             const uint32_t a_addr = smem_u32(smA), b_addr = smem_u32(smB);
             auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t acc_flag) {
                 if (kPair) umma_bf16_ss_pair(d, da, db, idesc, acc_flag);
@@ -381,17 +399,23 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + acc * BN;
                     for (int kb = 0; kb < nkb; ++kb) {
-                        mbar_wait(&ctl->b_full[st], ph, 5);
-                        tc_fence_after();
                         const int rem = D - kb * BK;
                         const int ksteps = rem >= BK ? BK / UK : (rem + UK - 1) / UK;
-                        for (int k = 0; k < ksteps; ++k) {
-                            const uint64_t da = make_sdesc_sw128(a_base + kb * A_KB_BYTES + k * (UK * 2));
-                            const uint64_t db = make_sdesc_sw128(b_addr + st * B_ST + k * (UK * 2));
-                            mma(d_tmem, da, db, (kb | k) != 0 ? 1u : 0u);
+                        for (int pb = 0; pb < npl; ++pb) {
+                            mbar_wait(&ctl->b_full[st], ph, 5);
+                            tc_fence_after();
+                            // split tier: the e_hi stage meets z_hi and z_lo, the e_lo stage z_hi only (z_lo.e_lo is
+                            // below the tier's 2^-16 error budget)
+                            const int npa = pb == 0 ? npl : 1;
+                            for (int pa = 0; pa < npa; ++pa)
+                                for (int k = 0; k < ksteps; ++k) {
+                                    const uint64_t da = make_sdesc_sw128(a_base + (pa * nkb + kb) * A_KB_BYTES + k * (UK * 2));
+                                    const uint64_t db = make_sdesc_sw128(b_addr + st * B_ST + k * (UK * 2));
+                                    mma(d_tmem, da, db, (kb | k | pb | pa) != 0 ? 1u : 0u);
+                                }
+                            commit(&ctl->b_empty[st]);         // stage reusable once these MMAs retire
+                            if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                         }
-                        commit(&ctl->b_empty[st]);             // stage reusable once these MMAs retire
-                        if (++st == (uint32_t)nstages) { st = 0; ph ^= 1; }
                     }
                     if (kMode == 3) {       // + [1,1,1,0..] x [h1,h2,h3,0..]^T = -||e||^2/2 into the same accumulator
                         mbar_wait(&ctl->b_full[st], ph, 5);
@@ -555,8 +579,8 @@ EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-// [rows, D] bf16, row stride ld elements; box = 64 features x box_rows rows, 128-byte swizzle, zero OOB fill.
-int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int D, int64_t ld, int box_rows) {
+// [rows, D] 16-bit elements, row stride ld elements; box = 64 features x box_rows rows, 128-byte swizzle, zero OOB fill.
+int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int D, int64_t ld, int box_rows, bool fp16 = false) {
     EncodeTiledFn enc = get_encode_fn();
     if (enc == nullptr) {
         set_error("cuTensorMapEncodeTiled entry point not available");
@@ -566,9 +590,9 @@ int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int D, int64_t ld,
     cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
     cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = enc(m, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                     const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (CUresult %d) rows=%lld D=%d ld=%lld box_rows=%d", (int)r,
                   (long long)rows, D, (long long)ld, box_rows);
@@ -604,13 +628,21 @@ int make_tmap_aug(CUtensorMap* m, const void* base, int K_pad) {
 bool assign_tc_supported(int64_t N, int D, int64_t ldz, int K) {
     return N > 0 && N < (int64_t(1) << 31) - BM && K > 0 && D >= 8 && D % 8 == 0 && D <= 512 && ldz % 8 == 0;
 }
+// split fp32 tier: two planes of the slab must leave room for the ring (D <= 256), plane offsets must fit a TMA coordinate
+bool assign_tc_split_supported(int64_t N, int D, int K) {
+    return N > 0 && N < (int64_t(1) << 30) - BM && K > 0 && K < (1 << 29) && D >= 8 && D % 8 == 0 && D <= 256;
+}
 
+// kind: VQ_SEARCH_BF16 (bf16 z, bf16 shadow), VQ_SEARCH_F16 (fp16 z, fp16 shadow), VQ_SEARCH_F32 (split tier: z16 is the
+// staged [2][N][D] bf16 hi / lo image of z with ldz == D, E16 the [2][K_pad][D] hi / lo shadow, norms of the fp32 rows)
 int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const void* E_bf16, const float* e_norm2,
-                     int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st) {
-    VQ_REQUIRE(assign_tc_supported(N, D, ldz, K), "vq_assign(bf16): unsupported shape N=%lld D=%d ldz=%lld K=%d",
-               (long long)N, D, (long long)ldz, K);
+                     int K, int kind, int32_t* idx, float* smin, Presort ps, cudaStream_t st) {
+    const bool split = kind == VQ_SEARCH_F32, fp16 = kind == VQ_SEARCH_F16;
+    const int planes = split ? 2 : 1;
+    VQ_REQUIRE(assign_tc_supported(N, D, ldz, K) && (!split || (assign_tc_split_supported(N, D, K) && ldz == D)),
+               "vq_assign(tensor core): unsupported shape N=%lld D=%d ldz=%lld K=%d", (long long)N, D, (long long)ldz, K);
     VQ_REQUIRE((reinterpret_cast<uintptr_t>(z_bf16) & 15) == 0 && (reinterpret_cast<uintptr_t>(E_bf16) & 15) == 0,
-               "vq_assign(bf16): z and E_bf16 must be 16-byte aligned");
+               "vq_assign(tensor core): z and the codebook shadow must be 16-byte aligned");
     const int nkb = (D + BK - 1) / BK;
     const int num_nb = (K + BN - 1) / BN;
     // The product build reads nothing from the environment: epilogue warps, epilogue mode and pairing follow the shape.
@@ -654,7 +686,7 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     //   norms go to shared memory when K <= 8192 and that still leaves >= 3 ring stages;
     //   the slab is double-buffered when that still leaves >= 4 ring stages.
     const int park_bytes = 2 * epi_warps * 32 * 16;
-    const int a_bytes = nkb * A_KB_BYTES;
+    const int a_bytes = planes * nkb * A_KB_BYTES;
     const int norm_bytes = num_nb * BN * 4;
     const int b_st = pair ? B_ST_BYTES / 2 : B_ST_BYTES;           // a pair CTA holds half of every codebook stage
     const int max_stages = pair ? MAX_STAGES : 6;
@@ -671,15 +703,27 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
         if (nstages >= 3 || mode == 0) break;
         mode = mode == 3 ? 2 : 0;                      // not enough room for the ring: fall back to a leaner mode
     }
-    VQ_REQUIRE(nstages >= 2, "vq_assign(bf16): D=%d leaves no room for the codebook ring", D);
+    VQ_REQUIRE(nstages >= 2, "vq_assign(tensor core): D=%d leaves no room for the codebook ring", D);
     const size_t smem_total = 1024 + (size_t)nabuf * a_bytes + (size_t)nstages * b_st +
                               (norm_smem ? norm_bytes : 0) + extra + sizeof(Ctl);
 
     CUtensorMap tm_z, tm_e, tm_aug;
-    int rc = make_tmap(&tm_z, z_bf16, N, D, ldz, BM);
+    const int K_pad = num_nb * BN;
+    int rc = make_tmap(&tm_z, z_bf16, planes * N, D, ldz, BM, fp16);
     if (rc != VQ_OK) return rc;
-    rc = make_tmap(&tm_e, E_bf16, K, D, D, pair ? BN / 2 : BN);
+    rc = make_tmap(&tm_e, E_bf16, split ? (int64_t)2 * K_pad : K, D, D, pair ? BN / 2 : BN, fp16);
     if (rc != VQ_OK) return rc;
+    OperandKind ok;
+    // [4,6) D = f32; [7,10) A format, [10,13) B format: 0 = f16, 1 = bf16; K-major both; [17,23) N >> 3; [24,29) M >> 4
+    ok.idesc = (1u << 4) | (fp16 ? 0u : (1u << 7) | (1u << 10)) | (static_cast<uint32_t>(BN >> 3) << 17) |
+               (static_cast<uint32_t>((pair ? 2 * BM : BM) >> 4) << 24);
+    // A-side partner of the norm image (vq_ema.cu: write_aug): bf16 pieces sum with weights (1, 1, 1); fp16 pieces carry
+    // the weights (2^8, 2^-4, 2^-14) so that -||e||^2/2 keeps 24 significant bits from 1e-11 up to 1.6e7
+    ok.ones01 = fp16 ? 0x2C005C00u : 0x3F803F80u;
+    ok.ones2 = fp16 ? 0x00000400u : 0x00003F80u;
+    ok.planes = planes;
+    ok.a_plane_rows = (int)N;
+    ok.b_plane_rows = K_pad;
     if (pair && mode == 3) {
         rc = make_tmap_aug(&tm_aug, e_norm2 + num_nb * BN, num_nb * BN);
         if (rc != VQ_OK) return rc;
@@ -689,10 +733,10 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
 
 #ifdef VQ_TUNING
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
-                 int32_t*, float*, int, const Presort);
+                 const OperandKind, int32_t*, float*, int, const Presort);
 #else
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
-                 int32_t*, float*, const Presort);
+                 const OperandKind, int32_t*, float*, const Presort);
 #endif
 #define VQ_PICK3(NS, EW, P)                                                                       \
     (mode == 3 ? assign_tc_kernel<false, EW, 3, P> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P>  \
@@ -767,9 +811,9 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
         cfg.numAttrs = na;
     }
 #ifdef VQ_TUNING
-    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, dbg, ps);
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, ok, idx, smin, dbg, ps);
 #else
-    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, idx, smin, ps);
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_z, tm_e, tm_aug, e_norm2, N, K, D, nkb, nstages, nabuf, ok, idx, smin, ps);
 #endif
     if (le != cudaSuccess && pair && attempt == 0) {  // cluster launch refused: fall back to the single-CTA kernel for good
         (void)cudaGetLastError();
@@ -782,7 +826,7 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     count_launch();
     return VQ_OK;
   }
-    set_error("vq_assign(bf16): kernel launch failed");
+    set_error("vq_assign(tensor core): kernel launch failed");
     return VQ_ERR_CUDA;
 }
 

@@ -49,11 +49,13 @@ struct Presort {
     int* start;   // [K+1] exclusive scan of hist
     int* done;    // [1]   blocks finished
 };
-int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const void* E_bf16, const float* e_norm2,
-                     int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st);
+int launch_assign_tc(const void* z16, int64_t N, int D, int64_t ldz, const void* E16, const float* e_norm2,
+                     int K, int kind, int32_t* idx, float* smin, Presort ps, cudaStream_t st);
+bool assign_tc_split_supported(int64_t N, int D, int K);
+int launch_split_bf16(const void* src, int in_dtype, int64_t N, int D, int64_t ld, void* dst_planes, cudaStream_t st);
 int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32,
                        const float* e_norm2, int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st);
-int launch_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, cudaStream_t st);
+int launch_cast_bf16(const void* src, int in_dtype, int64_t N, int D, int64_t ld, void* dst, cudaStream_t st);
 int launch_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, cudaStream_t st);
 size_t knn_workspace_bytes(int64_t N, int C);
 int launch_knn_topk(const float* X, int64_t N, int C, const float* coords, const int32_t* patch, float pos_min_spatial,
@@ -69,12 +71,14 @@ struct WsLayout {
     size_t scal, zbf16, cnt, start, cursor, perm, rank, partial, chunk_cnt, dpart, total;
     int rows_per_chunk, nchunks;
 };
-WsLayout ws_layout(int64_t N, int K, int D, int in_dtype);
+WsLayout ws_layout(int64_t N, int K, int D, int in_dtype, int search);     // search < 0: the VQ_SEARCH_BF16 sizing
 // optional by-products of the gather pass: the indices widened to int64 (the torch-facing dtype) and the scaled loss
 struct PassExtra {
     int64_t* idx64;      // [N] or NULL
     float* loss_out;     // [1] or NULL: sq_err_sum (after this call) * loss_scale
     float loss_scale;
+    int idx64_pre;       // set by the launcher: idx64 was already written in natural row order (coalesced) by the scatter
+                         // kernel; the pass only rewrites rows it canonicalises (non-finite latents)
 };
 int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx, const float* E_f32,
                        int K, void* q_out, int64_t ldq, float* sq_err_sum, float* code_cnt, float* code_sum,

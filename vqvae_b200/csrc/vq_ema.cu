@@ -4,6 +4,7 @@
 // Required by: scripts/train_vqvae.py:191-194,433-436 (quantizer="ema", ema_decay, ema_eps);
 // scripts/train_vqvae.py:92,197-198 and scripts/export_codebook.py:124-128 (usage); scripts/train_vqvae.py:357
 // (perplexity).  Definitions: SURVEY.md 8(a-7 .. a-9).
+#include <cuda_fp16.h>
 #include <math_constants.h>
 
 #include "vq_common.cuh"
@@ -184,12 +185,25 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
 // into three bf16 pieces (h1 + h2 + h3 reproduces the fp32 value), laid out as the canonical no-swizzle K-major UMMA
 // operand [256 codes x 16] (core matrix = 8 rows x 16 B; group of 8 rows g at g*256, second K half at +128).  The
 // tensor-core search multiplies it by a constant [1,1,1,0..] block so the accumulator already holds z.e - ||e||^2/2.
-__device__ __forceinline__ void write_aug(float* e_norm2, int norm_elems, int k, float nrm, bool pad) {
+// fp16 shadow (VQ_SEARCH_F16): the pieces are fp16 and carry the weights (2^8, 2^-4, 2^-14) of the A-side partner row
+// (vq_assign_tc.cu: OperandKind::ones*): p1 = fp16(h 2^-8), p2 = fp16((h - 2^8 p1) 2^4), p3 = fp16((.. - 2^-4 p2) 2^14);
+// every residual is exact in fp32, so 2^8 p1 + 2^-4 p2 + 2^-14 p3 keeps 24 significant bits of h for 1e-11 <= |h| <= 1.6e7
+// (fp16 alone would overflow at ||e||^2 = 131008 and lose bits below 1e-4).
+__device__ __forceinline__ void write_aug(float* e_norm2, int norm_elems, int k, float nrm, bool pad, bool fp16) {
     uint8_t* img = reinterpret_cast<uint8_t*>(e_norm2 + norm_elems) + (size_t)(k >> 8) * 8192 + ((k & 255) >> 3) * 256 +
                    (k & 7) * 16;
     uint4 lo = make_uint4(0u, 0u, 0u, 0u);
     if (pad) {
-        lo.x = 0xFF80u;                                    // bf16 -inf: a padding code never wins the arg-max
+        lo.x = fp16 ? 0xFC00u : 0xFF80u;                   // -inf: a padding code never wins the arg-max
+    } else if (fp16) {
+        const float h = -0.5f * nrm;
+        const __half p1 = __float2half_rn(h * 0.00390625f);
+        const float r1 = h - __half2float(p1) * 256.0f;
+        const __half p2 = __float2half_rn(r1 * 16.0f);
+        const float r2 = r1 - __half2float(p2) * 0.0625f;
+        const __half p3 = __float2half_rn(r2 * 16384.0f);
+        lo.x = (uint32_t)__half_as_ushort(p1) | ((uint32_t)__half_as_ushort(p2) << 16);
+        lo.y = (uint32_t)__half_as_ushort(p3);
     } else {
         const float h = -0.5f * nrm;
         const __nv_bfloat16 h1 = __float2bfloat16_rn(h);
@@ -203,7 +217,9 @@ __device__ __forceinline__ void write_aug(float* e_norm2, int norm_elems, int k,
     *reinterpret_cast<uint4*>(img + 128) = make_uint4(0u, 0u, 0u, 0u);
 }
 
-// one warp per code row.  do_ema: decay step + Laplace-normalised codebook row; always: refresh bf16 shadow + norm.
+// one warp per code row.  do_ema: decay step + Laplace-normalised codebook row; always: refresh the search shadow + norm.
+// The shadow follows the search kind: bf16 rows (VQ_SEARCH_BF16), fp16 rows (VQ_SEARCH_F16), or -- VQ_SEARCH_F32 with a
+// shadow -- the hi / lo bf16 planes [2][norm_elems][D] of the split tensor-core tier (pad rows zero).
 // kPeer: the per-code sums are added over the ranks' buffers (peer loads) in rank order.
 template <bool kPeer>
 __global__ void __launch_bounds__(256)
@@ -216,11 +232,17 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
     const int lane = threadIdx.x & 31;
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (k >= norm_elems) return;
+    const bool f16 = search == VQ_SEARCH_F16, split = search == VQ_SEARCH_F32 && E_bf16 != nullptr;
     if (k >= K) {
         if (lane == 0) {
             e_norm2[k] = CUDART_INF_F;
-            write_aug(e_norm2, norm_elems, k, 0.f, true);
+            write_aug(e_norm2, norm_elems, k, 0.f, true, f16);
         }
+        if (split)
+            for (int d = lane; d < D; d += 32) {
+                E_bf16[(int64_t)k * D + d] = __float2bfloat16_rn(0.f);
+                E_bf16[((int64_t)norm_elems + k) * D + d] = __float2bfloat16_rn(0.f);
+            }
         return;
     }
     const float omg = 1.0f - decay;
@@ -266,16 +288,24 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
             } else {
                 ev = E[o];
             }
-            const __nv_bfloat16 eb = __float2bfloat16_rn(ev);
-            if (E_bf16 != nullptr) E_bf16[o] = eb;
-            const float en = search == VQ_SEARCH_BF16 ? __bfloat162float(eb) : ev;
+            float en = ev;                        // the value whose norm the search adds: what the MMA operand holds
+            if (f16) {
+                const __half eh = __float2half_rn(ev);
+                if (E_bf16 != nullptr) reinterpret_cast<__half*>(E_bf16)[o] = eh;
+                en = __half2float(eh);
+            } else {
+                const __nv_bfloat16 eb = __float2bfloat16_rn(ev);
+                if (E_bf16 != nullptr) E_bf16[o] = eb;
+                if (search == VQ_SEARCH_BF16) en = __bfloat162float(eb);
+                else if (split) E_bf16[(int64_t)norm_elems * D + o] = __float2bfloat16_rn(ev - __bfloat162float(eb));
+            }
             nrm = fmaf(en, en, nrm);
         }
     }
     nrm = warp_sum(nrm);
     if (lane == 0) {
         e_norm2[k] = nrm;
-        write_aug(e_norm2, norm_elems, k, nrm, false);
+        write_aug(e_norm2, norm_elems, k, nrm, false, f16);
     }
 }
 
@@ -368,6 +398,10 @@ int launch_backward(const void* z, const void* q, const void* gq, int64_t N, int
         backward_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(z), static_cast<const float*>(q),
                                                        static_cast<const float*>(gq), N, D, ldz, grad_loss, coef,
                                                        static_cast<float*>(gz));
+    else if (dtype == VQ_DT_F16)
+        backward_kernel<__half><<<blocks, 256, 0, st>>>(static_cast<const __half*>(z), static_cast<const __half*>(q),
+                                                        static_cast<const __half*>(gq), N, D, ldz, grad_loss, coef,
+                                                        static_cast<__half*>(gz));
     else
         backward_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
             static_cast<const __nv_bfloat16*>(z), static_cast<const __nv_bfloat16*>(q),

@@ -11,6 +11,7 @@
 // Required by: scripts/export_codebook.py:104 (gather from [K, D]); frl/config/frl_model_v0.yaml:35 (straight
 // through); frl/config/frl_bindings_v0.yaml:887-891 (commitment + codebook terms); scripts/train_vqvae.py:433-436
 // (EMA statistics).  Definitions: SURVEY.md 8(a-2 .. a-5).
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 #include "vq_common.cuh"
@@ -147,11 +148,14 @@ scan_scatter_smem_kernel(const int32_t* __restrict__ idx, int64_t N, int K, int 
 // kernel above it clears the statistics buffers on the way.
 // kVec: four consecutive rows per thread (idx and rank read as int4), one thread per group -- every load of the
 // idx -> start -> perm chain is in flight at once instead of a latency-bound loop (12.9 -> ~5 us at C2).
+// idx64 (nullable): the indices widened to int64 for the torch-facing module, written HERE because this kernel walks the
+// rows in natural order -- 32 coalesced bytes per thread -- whereas the pass visits them in code-sorted order and paid
+// 18 us at C2 (12 % of its time) for 1.3 M scattered 8-byte stores.
 template <bool kVec>
 __global__ void __launch_bounds__(256)
 scatter_ranked_kernel(const int32_t* __restrict__ idx, const int* __restrict__ rank, int64_t N, int K,
                       const int* __restrict__ start, int32_t* __restrict__ perm, float4* __restrict__ zero_a,
-                      int64_t na4, float* __restrict__ zero_b, int nb) {
+                      int64_t na4, float* __restrict__ zero_b, int nb, int64_t* __restrict__ idx64) {
     pdl_wait();
     pdl_trigger();
     const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, nth = (int64_t)gridDim.x * 256;
@@ -160,24 +164,34 @@ scatter_ranked_kernel(const int32_t* __restrict__ idx, const int* __restrict__ r
         for (int64_t g = tid; g < n4; g += nth) {
             const int4 c = __ldcs(reinterpret_cast<const int4*>(idx) + g);
             const int4 r = __ldcs(reinterpret_cast<const int4*>(rank) + g);
-            const int cc[4] = {c.x, c.y, c.z, c.w};
+            int cc[4] = {c.x, c.y, c.z, c.w};
             const int rr[4] = {r.x, r.y, r.z, r.w};
             int st[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) st[j] = __ldg(start + ((unsigned)cc[j] < (unsigned)K ? cc[j] : 0));
+            for (int j = 0; j < 4; ++j) {
+                if ((unsigned)cc[j] >= (unsigned)K) cc[j] = 0;
+                st[j] = __ldg(start + cc[j]);
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) perm[st[j] + rr[j]] = (int32_t)(g * 4 + j);
+            if (idx64 != nullptr) {           // 16-byte aligned (checked by the launcher): two streaming 16-byte stores
+                longlong2* o = reinterpret_cast<longlong2*>(idx64 + g * 4);
+                __stcs(o, make_longlong2(cc[0], cc[1]));
+                __stcs(o + 1, make_longlong2(cc[2], cc[3]));
+            }
         }
         for (int64_t n = (n4 << 2) + tid; n < N; n += nth) {
             int c = idx[n];
             if ((unsigned)c >= (unsigned)K) c = 0;
             perm[__ldg(start + c) + rank[n]] = (int32_t)n;
+            if (idx64 != nullptr) idx64[n] = c;
         }
     } else {
         for (int64_t n = tid; n < N; n += nth) {
             int c = idx[n];
             if ((unsigned)c >= (unsigned)K) c = 0;
             perm[__ldg(start + c) + rank[n]] = (int32_t)n;
+            if (idx64 != nullptr) idx64[n] = c;
         }
     }
     for (int64_t i = tid; i < na4; i += nth) zero_a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -306,6 +320,33 @@ template <> struct VecIO<__nv_bfloat16> {
         uint32_t acc = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) acc |= (w[i] & 0x7f807f80u) + 0x00800080u;
+        return (acc & 0x80008000u) != 0;
+    }
+};
+template <> struct VecIO<__half> {      // fp16 latents: the reference script's default autocast dtype
+    static constexpr int EPV = 8;
+    __device__ static __forceinline__ void unpack(const int4& v, float (&f)[8]) {
+        const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+            f[2 * i] = t.x; f[2 * i + 1] = t.y;
+        }
+    }
+    __device__ static __forceinline__ int4 pack(const float (&f)[8]) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __half2 h = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+            w[i] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        return make_int4((int)w[0], (int)w[1], (int)w[2], (int)w[3]);
+    }
+    __device__ static __forceinline__ bool nonfinite(const int4& v) {   // any fp16 with an all-ones exponent (5 bits)
+        const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+        uint32_t acc = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc |= (w[i] & 0x7c007c00u) + 0x04000400u;
         return (acc & 0x80008000u) != 0;
     }
 };
@@ -598,7 +639,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
                         }
                     }
                     ++cnt;
-                    if (X.idx64 != nullptr && lg == 0) X.idx64[r] = c;
+                    if (X.idx64 != nullptr && !X.idx64_pre && lg == 0) X.idx64[r] = c;
                 } else {
                     // non-finite latent row: idx := 0, q := E[0], no contribution to loss or statistics
 #pragma unroll
@@ -835,7 +876,7 @@ int launch_pass_dispatch(int V, const void* z, int64_t N, int D, int64_t ldz, in
 }  // namespace
 
 // Workspace carve-up shared by vq_workspace_bytes and the launchers.
-WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
+WsLayout ws_layout(int64_t N, int K, int D, int in_dtype, int search) {
     auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
     WsLayout L;
     size_t o = 0;
@@ -853,7 +894,11 @@ WsLayout ws_layout(int64_t N, int K, int D, int in_dtype) {
     L.nchunks = (int)ceil_div64(N, L.rows_per_chunk);
     L.chunk_cnt = o; o += al((size_t)L.nchunks * K * 4);
     L.dpart = o;     o += al((size_t)(ceil_div64(N, LG) + K + 1) * D * 4);   // deterministic mode: one slot per run
-    L.zbf16 = o;     o += in_dtype == VQ_DT_F32 ? al((size_t)N * D * 2) : 0;   // fp32 latents staged as bf16 for the search
+    // staging for the tensor-core searches of non-native latents (LAST region: nothing else moves with the search kind):
+    // the split fp32 tier takes two bf16 planes of any latent dtype, fp32 / fp16 latents under VQ_SEARCH_BF16 take one
+    const int planes = search == VQ_SEARCH_F32 ? (assign_tc_split_supported(N, D, K) ? 2 : 0)
+                                               : ((search == VQ_SEARCH_BF16 || search < 0) && in_dtype != VQ_DT_BF16 ? 1 : 0);
+    L.zbf16 = o;     o += al((size_t)N * D * 2 * planes);
     L.total = o;
     return L;
 }
@@ -877,7 +922,7 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         return VQ_OK;
     }
     VQ_REQUIRE(ws != nullptr, "vq_gather_st_loss_scatter: workspace required");
-    const WsLayout L = ws_layout(N, K, D, in_dtype);
+    const WsLayout L = ws_layout(N, K, D, in_dtype, -1);         // the pass uses none of the search's staging
     uint8_t* w = static_cast<uint8_t*>(ws);
     int* cnt_i = reinterpret_cast<int*>(w + L.cnt);
     int* start = reinterpret_cast<int*>(w + L.start);
@@ -888,7 +933,7 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
     int* chunk_cnt = reinterpret_cast<int*>(w + L.chunk_cnt);
     bool stats_cleared = false;
 
-    const int es = in_dtype == VQ_DT_F32 ? 4 : 2;
+    const int es = in_dtype == VQ_DT_F32 ? 4 : 2;                // bf16 and fp16 rows are both 2-byte
     const int epv = 16 / es;
     const bool vec_ok = D % epv == 0 && (ldz * es) % 16 == 0 && (ldq * es) % 16 == 0 &&
                         (reinterpret_cast<uintptr_t>(z) & 15) == 0 && (reinterpret_cast<uintptr_t>(q_out) & 15) == 0 &&
@@ -918,6 +963,10 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
             pass_generic_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const float*>(z), N, D, ldz, idx,
                                                                          E_f32, K, static_cast<float*>(q_out), ldq,
                                                                          part, code_cnt, code_sum, stat_kind, X);
+        else if (in_dtype == VQ_DT_F16)
+            pass_generic_kernel<__half><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const __half*>(z), N, D, ldz, idx,
+                                                                          E_f32, K, static_cast<__half*>(q_out), ldq,
+                                                                          part, code_cnt, code_sum, stat_kind, X);
         else
             pass_generic_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(
                 static_cast<const __nv_bfloat16*>(z), N, D, ldz, idx, E_f32, K, static_cast<__nv_bfloat16*>(q_out), ldq,
@@ -940,7 +989,8 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                 dpart = reinterpret_cast<float*>(w + L.dpart);
             } else if (presorted) {
                 const bool zero_here = !accum && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 && ((size_t)K * D) % 4 == 0;
-                const bool vec4 = (reinterpret_cast<uintptr_t>(idx) & 15) == 0;
+                const bool vec4 = (reinterpret_cast<uintptr_t>(idx) & 15) == 0 &&
+                                  (reinterpret_cast<uintptr_t>(X.idx64) & 15) == 0;
                 const int64_t work = vec4 ? ceil_div64(N, 4) : N;
                 const int64_t want = ceil_div64(work > (int64_t)K * D / 8 ? work : (int64_t)K * D / 8, 256);
                 const int gs = (int)(want < (int64_t)sm_count() * 32 ? (want < 1 ? 1 : want) : (int64_t)sm_count() * 32);
@@ -948,9 +998,10 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                 float4* za = reinterpret_cast<float4*>(code_sum);
                 const int64_t na4 = zero_here ? (int64_t)K * D / 4 : 0;
                 VQ_CHECK_CUDA(launch_pdl(PDL_SCATTER, vec4 ? scatter_ranked_kernel<true> : scatter_ranked_kernel<false>, dim3(gs), dim3(256),
-                                         0, st, idx, rank, N, K, start, perm, za, na4, code_cnt, zero_here ? K : 0));
+                                         0, st, idx, rank, N, K, start, perm, za, na4, code_cnt, zero_here ? K : 0, X.idx64));
                 count_launch(1);
                 stats_cleared = zero_here;
+                X.idx64_pre = X.idx64 != nullptr;
             } else if ((size_t)K * 12 <= 200 * 1024 && (reinterpret_cast<uintptr_t>(code_sum) & 15) == 0 &&
                        ((size_t)K * D) % 4 == 0) {
                 // shared-memory privatised counting sort, 2 launches: block b owns R consecutive rows; the second
@@ -990,6 +1041,9 @@ int launch_gather_pass(const void* z, int in_dtype, int64_t N, int D, int64_t ld
         if (in_dtype == VQ_DT_F32)
             launch_pass_dispatch<float>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts, code_cnt,
                                         code_sum, dpart, stat_kind, done, sq_err_sum, X, st);
+        else if (in_dtype == VQ_DT_F16)
+            launch_pass_dispatch<__half>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts, code_cnt,
+                                         code_sum, dpart, stat_kind, done, sq_err_sum, X, st);
         else
             launch_pass_dispatch<__nv_bfloat16>(V, z, N, D, ldz, idx, perm_arg, E_f32, K, q_out, ldq, part, &nparts,
                                                 code_cnt, code_sum, dpart, stat_kind, done, sq_err_sum, X, st);

@@ -12,17 +12,23 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib
-from ._lib import (VQ_DT_BF16, VQ_DT_F32, VQ_SEARCH_BF16, VQ_SEARCH_F32, VQ_STAT_SUM_RESID, VQ_STAT_SUM_Z, check)
+from ._lib import (VQ_DT_BF16, VQ_DT_F16, VQ_DT_F32, VQ_SEARCH_BF16, VQ_SEARCH_F16, VQ_SEARCH_F32, VQ_SEARCH_SIMT,
+                   VQ_STAT_SUM_RESID, VQ_STAT_SUM_Z, check)
 
-SEARCH_MODES = {"bf16": VQ_SEARCH_BF16, "fp32": VQ_SEARCH_F32}
+# search kinds (include/vq_b200.h): "bf16" / "fp16" = tensor-core search on operands of that type; "fp32" = the 1e-5 tier
+# (split-operand tensor-core search when the shape allows and the split shadow is given, CUDA-core kernel otherwise);
+# "fp32_simt" forces the CUDA-core kernel
+SEARCH_MODES = {"bf16": VQ_SEARCH_BF16, "fp32": VQ_SEARCH_F32, "fp16": VQ_SEARCH_F16,
+                "fp32_simt": VQ_SEARCH_F32 | VQ_SEARCH_SIMT}
+_DTYPES = {torch.bfloat16: VQ_DT_BF16, torch.float32: VQ_DT_F32, torch.float16: VQ_DT_F16}
+SHADOW_DTYPE = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.bfloat16, "fp32_simt": torch.bfloat16}
 
 
 def _dt(t: torch.Tensor) -> int:
-    if t.dtype == torch.bfloat16:
-        return VQ_DT_BF16
-    if t.dtype == torch.float32:
-        return VQ_DT_F32
-    raise TypeError(f"vqvae_b200 kernels take bfloat16 or float32 latents, got {t.dtype}")
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"vqvae_b200 kernels take bfloat16, float16 or float32 latents, got {t.dtype}") from None
 
 
 class _On:
@@ -80,11 +86,25 @@ def norm_elems(K: int) -> int:
     return _lib.load().vq_norm_elems(K)
 
 
-def workspace_bytes(N: int, K: int, D: int, dtype: torch.dtype) -> int:
+def workspace_bytes(N: int, K: int, D: int, dtype: torch.dtype, search: Optional[str] = None) -> int:
+    """Scratch bytes of one step; `search` defaults to the kind the dtype takes natively (bf16 / fp16 latents: their own
+    tensor-core search, fp32 latents: "fp32")."""
     out = C.c_size_t(0)
-    dt = VQ_DT_BF16 if dtype == torch.bfloat16 else VQ_DT_F32
-    check(_lib.load().vq_workspace_bytes(N, K, D, dt, C.byref(out)), "vq_workspace_bytes")
+    if search is None:
+        search = {torch.bfloat16: "bf16", torch.float16: "fp16"}.get(dtype, "fp32")
+    check(_lib.load().vq_workspace_bytes(N, K, D, _DTYPES[dtype], SEARCH_MODES[search] & 3, C.byref(out)),
+          "vq_workspace_bytes")
     return int(out.value)
+
+
+def shadow_elems(K: int, D: int, search: str) -> int:
+    """16-bit elements the search shadow holds for this search kind (K * D; hi + lo planes [2][K_pad][D] for "fp32")."""
+    return int(_lib.load().vq_shadow_elems(K, D, SEARCH_MODES[search] & 3))
+
+
+def new_shadow(K: int, D: int, search: str, device) -> torch.Tensor:
+    """Flat shadow buffer of the right size and element type for `search` (filled by prepare_codebook / ema_update)."""
+    return torch.empty(shadow_elems(K, D, search), dtype=SHADOW_DTYPE[search], device=device)
 
 
 def set_pdl_mask(mask: int) -> int:
@@ -102,12 +122,21 @@ def launch_count() -> int:
     return int(_lib.load().vq_launch_count())
 
 
+def _check_shadow(shadow: Optional[torch.Tensor], K: int, D: int, search: str) -> None:
+    if shadow is None:
+        return
+    if shadow.element_size() != 2 or not shadow.is_contiguous() or shadow.numel() < shadow_elems(K, D, search):
+        raise ValueError(f"search shadow for search={search!r} must be a contiguous 16-bit tensor of at least "
+                         f"{shadow_elems(K, D, search)} elements (ops.new_shadow), got {tuple(shadow.shape)} {shadow.dtype}")
+
+
 def prepare_codebook(E: torch.Tensor, search: str, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor) -> None:
     with _On(E, E_bf16, e_norm2) as on:
         K, D = E.shape
         assert E.dtype == torch.float32 and E.is_contiguous()
         assert e_norm2.dtype == torch.float32 and e_norm2.numel() >= norm_elems(K)
-        check(_lib.load().vq_prepare_codebook(_ptr(E), K, D, SEARCH_MODES[search], _ptr(E_bf16), _ptr(e_norm2),
+        _check_shadow(E_bf16, K, D, search)
+        check(_lib.load().vq_prepare_codebook(_ptr(E), K, D, SEARCH_MODES[search] & 3, _ptr(E_bf16), _ptr(e_norm2),
                                               on.stream), "vq_prepare_codebook")
 
 
@@ -167,8 +196,9 @@ def ema_update(E: torch.Tensor, ema_cnt: Optional[torch.Tensor], ema_sum: Option
         K, D = E.shape
         assert usage_total.dtype == torch.int64 and steps_since_used.dtype == torch.int32 and n_dead.dtype == torch.int32
         assert perplexity.dtype == torch.float32
+        _check_shadow(E_bf16, K, D, search)
         check(_lib.load().vq_ema_update(_ptr(E), _ptr(ema_cnt), _ptr(ema_sum), _ptr(code_cnt), _ptr(code_sum), K, D,
-                                        float(decay), float(eps), int(bool(do_ema)), SEARCH_MODES[search], _ptr(E_bf16),
+                                        float(decay), float(eps), int(bool(do_ema)), SEARCH_MODES[search] & 3, _ptr(E_bf16),
                                         _ptr(e_norm2), _ptr(usage_total), _ptr(steps_since_used), _ptr(perplexity),
                                         _ptr(n_dead), int(dead_after), int(bool(update_usage)), _ptr(ws), on.stream),
               "vq_ema_update")
@@ -220,8 +250,9 @@ def ema_update_dp(E: torch.Tensor, ema_cnt: torch.Tensor, ema_sum: torch.Tensor,
         world = len(peer_stats)
         ps = (C.c_void_p * world)(*[int(p) for p in peer_stats])
         pf = (C.c_void_p * world)(*[int(p) for p in peer_flags])
+        _check_shadow(E_bf16, K, D, search)
         check(_lib.load().vq_ema_update_dp(_ptr(E), _ptr(ema_cnt), _ptr(ema_sum), K, D, float(decay), float(eps),
-                                           int(bool(do_ema)), SEARCH_MODES[search], _ptr(E_bf16), _ptr(e_norm2),
+                                           int(bool(do_ema)), SEARCH_MODES[search] & 3, _ptr(E_bf16), _ptr(e_norm2),
                                            _ptr(usage_total), _ptr(steps_since_used), _ptr(perplexity), _ptr(n_dead),
                                            int(dead_after), int(bool(update_usage)), _ptr(ws), ps, pf, world, int(rank),
                                            int(epoch), on.stream), "vq_ema_update_dp")

@@ -132,7 +132,10 @@ class VectorQuantizer(nn.Module):
     """Nearest-codebook quantiser with straight-through output, commitment/codebook loss and (in "ema"
     mode) an EMA codebook update, all on hand-written sm_100a kernels.
 
-    search: "auto" (bf16 latents -> bf16 tensor-core search, fp32 latents -> fp32 search), "bf16" or "fp32".
+    search: "auto" (bf16 / fp16 latents -> tensor-core search on operands of that type, fp32 latents -> the fp32 tier),
+        "bf16" (fp32 / fp16 latents are staged as bf16), "fp16" (fp16 latents only), "fp32" (the 1e-5 tier: split-operand
+        tensor-core search, three bf16 MMAs per product, CUDA cores where the shape does not fit) or "fp32_simt" (always
+        the CUDA-core kernel).
     deterministic: code-sorted visiting order reproducible run to run (stable counting sort).
     channel_first: forward takes [B, D, *spatial] (the live model's layout, frl/models/representation.py:317-334)
         and returns quantized in the same layout, indices [B, *spatial]; one transpose pass each way (a-0).
@@ -157,8 +160,8 @@ class VectorQuantizer(nn.Module):
         self.peer_timeout_s = peer_timeout_s
         if quantizer not in ("st", "ema"):
             raise ValueError(f"quantizer must be 'st' or 'ema', got {quantizer!r}")
-        if search not in ("auto", "bf16", "fp32"):
-            raise ValueError(f"search must be 'auto', 'bf16' or 'fp32', got {search!r}")
+        if search not in ("auto", "bf16", "fp16", "fp32", "fp32_simt"):
+            raise ValueError(f"search must be 'auto', 'bf16', 'fp16', 'fp32' or 'fp32_simt', got {search!r}")
         self.emb_dim, self.codebook_size = int(emb_dim), int(codebook_size)
         self.beta, self.quantizer = float(beta), quantizer
         self.ema_decay, self.ema_eps = float(ema_decay), float(ema_eps)
@@ -257,8 +260,9 @@ class VectorQuantizer(nn.Module):
 
     # ------------------------------------------------------------------ scratch management
     def _search_for(self, dtype: torch.dtype) -> str:
-        """"auto": half-precision latents (bf16, and fp16 -- the reference script's default autocast dtype,
-        scripts/train_vqvae.py:284-286) take the tensor-core search, fp32 latents the fp32 search.  An emb_dim the
+        """"auto": half-precision latents take the tensor-core search on operands of their own type (bf16 x bf16 shadow;
+        fp16 -- the reference script's default autocast dtype, scripts/train_vqvae.py:284-286 -- x fp16 shadow: no
+        staging pass, no cast), fp32 latents the fp32 tier (split-operand tensor-core search, CUDA cores for odd shapes).  An emb_dim the
         tensor-core kernel cannot take (not a multiple of 8, below 8 or above 512) goes to the fp32 kernel, which has no
         shape limits; only an explicit search="bf16" insists (and raises for such a shape)."""
         if self.search != "auto":
@@ -266,7 +270,7 @@ class VectorQuantizer(nn.Module):
         D = self.emb_dim
         if D % 8 != 0 or D < 8 or D > 512:
             return "fp32"
-        return "bf16" if dtype in (torch.bfloat16, torch.float16) else "fp32"
+        return {torch.bfloat16: "bf16", torch.float16: "fp16"}.get(dtype, "fp32")
 
     def _ensure_shadow(self, search: str) -> None:
         """(Re)build the bf16 copy and ||e||^2 the search reads if the codebook changed behind our back
@@ -276,18 +280,23 @@ class VectorQuantizer(nn.Module):
         if key == self._shadow_key:
             return
         K, D = E.shape
-        if self._E_bf16 is None or self._E_bf16.device != E.device:
-            self._E_bf16 = torch.empty((K, D), dtype=torch.bfloat16, device=E.device)
-            self._e_norm2 = torch.empty(ops.norm_elems(K), dtype=torch.float32, device=E.device)
+        if (self._E_bf16 is None or self._E_bf16.device != E.device or self._E_bf16.dtype != ops.SHADOW_DTYPE[search]
+                or self._E_bf16.numel() != ops.shadow_elems(K, D, search)):
+            # 16-bit image of the codebook in the search's operand type: bf16 rows, fp16 rows, or the hi / lo bf16 planes
+            # of the split fp32 tier
+            self._E_bf16 = ops.new_shadow(K, D, search, E.device)
+            if self._e_norm2 is None or self._e_norm2.device != E.device:
+                self._e_norm2 = torch.empty(ops.norm_elems(K), dtype=torch.float32, device=E.device)
         ops.prepare_codebook(E, search, self._E_bf16, self._e_norm2)
         self._shadow_key = key
 
-    def _workspace(self, N: int, dtype: torch.dtype) -> torch.Tensor:
-        need = self._ws_need.get((N, dtype))
-        if need is None:                              # one ctypes call per new (rows, dtype), not per step
+    def _workspace(self, N: int, dtype: torch.dtype, search: str = "bf16") -> torch.Tensor:
+        need = self._ws_need.get((N, dtype, search))
+        if need is None:                              # one ctypes call per new (rows, dtype, search), not per step
             if len(self._ws_need) > 64:
                 self._ws_need.clear()
-            need = self._ws_need[(N, dtype)] = ops.workspace_bytes(N, self.codebook_size, self.emb_dim, dtype)
+            need = self._ws_need[(N, dtype, search)] = ops.workspace_bytes(N, self.codebook_size, self.emb_dim, dtype,
+                                                                           search)
         dev = self.codebook.device
         if self._ws is None or self._ws.numel() < need or self._ws.device != dev:
             # zero-filled, and from here on used only by this module's presort / presorted calls: the counter region
@@ -340,7 +349,7 @@ class VectorQuantizer(nn.Module):
         and the scaled loss are by-products of the gather pass: no torch arithmetic on the path."""
         N, D = z2.shape
         K = self.codebook_size
-        ws = self._workspace(N, z2.dtype)
+        ws = self._workspace(N, z2.dtype, search)
         stats = self._stats_buffer()
         code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
         E = self.codebook.detach()
@@ -369,7 +378,7 @@ class VectorQuantizer(nn.Module):
             key = (N, z2.dtype, search, self.training, self.quantizer, self.deterministic, self.beta, self.ema_decay,
                    self.ema_eps, self.dead_after, self.codebook.data_ptr(),
                    self.ema_sum.data_ptr(), self._E_bf16.data_ptr() if self._E_bf16 is not None else 0,
-                   self._e_norm2.data_ptr(), self._workspace(N, z2.dtype).data_ptr(), self._stats_buffer().data_ptr(),
+                   self._e_norm2.data_ptr(), self._workspace(N, z2.dtype, search).data_ptr(), self._stats_buffer().data_ptr(),
                    dev.index)
             ent = self._graphs.get(key)
             if ent is None:
@@ -419,7 +428,7 @@ class VectorQuantizer(nn.Module):
         sloss = sout[nq + 8 * N:nq + 8 * N + 4].view(torch.float32)
         si32 = torch.empty(N, dtype=torch.int32, device=dev)
         ssq = torch.empty(1, dtype=torch.float32, device=dev)
-        self._workspace(N, z2.dtype)                 # sized before capture: the graph holds its address
+        self._workspace(N, z2.dtype, search)         # sized before capture: the graph holds its address
         self._stats_buffer()
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize(dev)
@@ -476,10 +485,8 @@ class VectorQuantizer(nn.Module):
             in_dtype = z.dtype
             z2 = z.reshape(-1, self.emb_dim)
             search = self._search_for(z2.dtype)
-            if z2.dtype not in (torch.bfloat16, torch.float32):
-                # fp16 autocast: gather, loss and statistics in fp32 on the widened values (cast back below); the SEARCH
-                # stages them as bf16 for the tensor core unless search="fp32" asks for the exact tier
-                z2 = z2.to(torch.float32)
+            if z2.dtype not in (torch.bfloat16, torch.float16, torch.float32):
+                z2 = z2.to(torch.float32)        # exotic dtypes only; bf16 / fp16 / fp32 rows go to the kernels as they are
             if z2.shape[0] > 1 and (z2.stride(1) != 1 or z2.stride(0) < self.emb_dim):
                 z2 = z2.contiguous()
             if torch.is_grad_enabled() and (z2.requires_grad or self.codebook.requires_grad):
@@ -511,7 +518,7 @@ class VectorQuantizer(nn.Module):
         if z_host.shape[-1] != self.emb_dim:
             raise ValueError(f"last dimension {z_host.shape[-1]} != emb_dim {self.emb_dim}")
         search = self._search_for(z_host.dtype)
-        if z_host.dtype not in (torch.bfloat16, torch.float32):
+        if z_host.dtype not in (torch.bfloat16, torch.float16, torch.float32):
             z_host = z_host.to(torch.float32)
         for name, t, dt in (("q_host", q_host, z_host.dtype), ("idx_host", idx_host, torch.int64)):
             if t is not None and (t.is_cuda or t.dtype != dt or not t.is_contiguous() or not t.is_pinned()):
@@ -559,7 +566,7 @@ class VectorQuantizer(nn.Module):
         loss = torch.zeros(1, dtype=torch.float32, device=dev)
         stats = self._stats_buffer()
         code_sum, code_cnt = stats[:K * D].view(K, D), stats[K * D:K * D + K]
-        ws = self._workspace(rows if N > 0 else 0, zh.dtype)
+        ws = self._workspace(rows if N > 0 else 0, zh.dtype, search)
         E = self.codebook.detach()
         kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
         copy.wait_stream(cur)                   # the fresh device buffers are not reused memory still in flight
@@ -615,7 +622,7 @@ class VectorQuantizer(nn.Module):
             in_dtype = z.dtype
             z3 = z.reshape(B, D, -1)
             search = self._search_for(z3.dtype)
-            if z3.dtype not in (torch.bfloat16, torch.float32):
+            if z3.dtype not in (torch.bfloat16, torch.float16, torch.float32):
                 z3 = z3.to(torch.float32)
             rows = _LayoutTranspose.apply(z3)                          # [B, S, D]
             q, loss, idx = _VQFunction.apply(rows.reshape(-1, D), self.codebook, self, search)
