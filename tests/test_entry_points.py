@@ -80,3 +80,76 @@ def test_short_training_run_and_export(tmp_path, quantizer, bf16):
     assert int(ck["model"]["quant.usage_total"].sum()) == 60 * 8 * 2 * 16 * 16
     assert export_codebook.main(["--ckpt", str(tmp_path / "ckpt_epoch002.pt"), "--out", str(tmp_path / "dec")]) == 0
     assert np.load(tmp_path / "dec.npz")["codes_K3"][:, 1].sum() == 60 * 8 * 2 * 16 * 16
+
+
+class _OracleOnCpu(torch.nn.Module):
+    """The CPU oracle standing in for `model.quant` inside the GPU model: latents go to the host (a differentiable copy),
+    the oracle runs there, results come back -- so that the SAME training step can be run with either quantiser."""
+
+    def __init__(self, ref):
+        super().__init__()
+        self.ref = ref
+
+    @property
+    def perplexity(self):
+        return self.ref.last_perplexity[0]
+
+    def forward(self, z):
+        q, loss, idx = self.ref(z.float().cpu())
+        return q.to(z.device), loss.to(z.device), idx.to(z.device)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("quantizer", ["ema", "st"])
+def test_training_steps_native_quantiser_vs_oracle_swapped_in(quantizer):
+    """the loop of scripts/train_vqvae.py:261-347 (model(batch) -> losses -> backward -> AdamW with
+    the codebook in its own weight_decay = 0 group) for 10 fp32 deterministic steps, once around the native quantiser and
+    once with the oracle swapped in for `model.quant`: per-step vq_loss, perplexity and the final codebook must agree."""
+    from oracle import vq_reference as R
+    import torch.nn.functional as F
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    K, D = 64, 32
+
+    def build(seed):
+        torch.manual_seed(seed)
+        return VQVAE(cont_dim=16, cat_vocab_sizes={"lc": 12}, emb_dim=D, codebook_size=K, hidden=32, quantizer=quantizer,
+                     search="fp32", deterministic=True, cuda_graph=False)
+    native = build(0).cuda().train()
+    swapped = build(0)
+    ref = R.VectorQuantizerOracle(D, K, beta=0.25, quantizer=quantizer).train()
+    ref.load_state_dict({k: v.clone() for k, v in swapped.quant.state_dict().items()}, strict=False)
+    swapped.quant = None
+    swapped = swapped.cuda().train()
+    swapped.quant = _OracleOnCpu(ref)                    # stays on the CPU
+    ds = SyntheticPatches(cont_dim=16, T=2, H=16, W=16, seed=3, device="cuda")
+
+    def make_opt(m, cb):
+        others = [p for n, p in m.named_parameters() if "quant" not in n]
+        groups = [{"params": others, "weight_decay": 1e-4}]
+        if cb is not None:
+            groups.append({"params": [cb], "weight_decay": 0.0})
+        return torch.optim.AdamW(groups, lr=1e-3, betas=(0.9, 0.95))
+    opt_n = make_opt(native, native.quant.codebook if quantizer == "st" else None)
+    opt_s = make_opt(swapped, ref.codebook if quantizer == "st" else None)
+    for step in range(10):
+        batch = ds.batch(4)
+        vals = []
+        for m, opt in ((native, opt_n), (swapped, opt_s)):
+            opt.zero_grad(set_to_none=True)
+            cont_pred, cat_logits, canopy_pred, vq_loss, pplx = m(batch)
+            loss = F.mse_loss(cont_pred, batch["cont"]) + vq_loss + F.mse_loss(canopy_pred, batch["canopy"])
+            for j, name in enumerate(ds.cat_names):
+                loss = loss + F.cross_entropy(cat_logits[name].reshape(-1, cat_logits[name].size(-1)),
+                                              batch["cat_target"][..., j].reshape(-1))
+            loss.backward()
+            opt.step()
+            vals.append((float(vq_loss), float(pplx), float(loss)))
+        (vn, pn, ln), (vs, ps, ls) = vals
+        assert abs(vn - vs) <= 5e-4 * abs(vs), (step, vn, vs)
+        assert abs(pn - ps) <= 5e-4 * ps, (step, pn, ps)
+        assert abs(ln - ls) <= 5e-4 * abs(ls), (step, ln, ls)
+    En, Es = native.quant.codebook.detach().cpu(), ref.codebook.detach()
+    assert float((En - Es).abs().max() / Es.abs().max()) <= 2e-3
+    used_n, used_s = native.quant.usage_total.cpu(), ref.usage_total
+    assert int(used_n.sum()) == int(used_s.sum()) and int((used_n != used_s).sum()) <= 2
