@@ -114,6 +114,21 @@ int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int
                               int deterministic, int64_t* idx64_out, float* loss_out, float loss_scale, void* ws,
                               vq_stream_t stream);
 
+/* The same pass for callers that cannot give the library a workspace of their own (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch lives in a file-scope __device__ array of VQ_NOALLOC_SCRATCH_BYTES inside the library (every
+ * GPU that loads the library holds it until the process exits); the call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating routine).  Limits: non-deterministic mode only, no VQ_STAT_PRESORTED, and the counting-sort scratch of the
+ * shape -- about 12 bytes per row + 12 bytes per code -- must fit: N up to ~340 000 rows at K = 8192; larger shapes
+ * return VQ_ERR_UNSUPPORTED with a message.  All calls on one GPU share the array: calls that overlap on the GPU (two
+ * streams without ordering) race; calls on one stream, or ordered by events, are fine (each call clears what it needs).
+ * Results equal vq_gather_st_loss_scatter(..., deterministic = 0, ...) on the same inputs. */
+#define VQ_NOALLOC_SCRATCH_BYTES (4 << 20)
+int vq_gather_st_loss_scatter_noalloc(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, int32_t* idx,
+                                      const float* E_f32, int K, void* q_out, int64_t ldq, float* sq_err_sum,
+                                      float* code_cnt /* [K] or NULL */, float* code_sum /* [K*D] or NULL */, int stat_kind,
+                                      int64_t* idx64_out, float* loss_out, float loss_scale, vq_stream_t stream);
+
 /* a-7..a-9 (after the cross-GPU reduce of code_cnt/code_sum, a-6):
  *   n_k <- g n_k + (1-g) cnt_k ; m_k <- g m_k + (1-g) sum_k ; n^_k = (n_k+eps)/(sum n + K eps) * sum n ;
  *   e_k <- m_k / n^_k ; then the search shadow (E_bf16, e_norm2) is refreshed in the same launch.

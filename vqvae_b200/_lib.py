@@ -23,6 +23,7 @@ VQ_SEARCH_WS_CLEAN = 512    # caller vouches that the workspace counters are zer
 VQ_SEARCH_PRESORT = 256     # vq_assign also leaves histogram / ranks / scan of idx in the workspace
 ABI_VERSION = 3
 MAX_PEERS, IPC_HANDLE_BYTES = 16, 64
+NOALLOC_SCRATCH_BYTES = 4 << 20
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 
@@ -40,6 +41,7 @@ SIGNATURES = {
     "vq_assign": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _p, _i, _i, _p, _p, _p, _p]),
     "vq_gather_st_loss_scatter": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _i, _p, _i, _i64, _p, _p, _p, _i, _i, _p, _p, _f,
                                        _p, _p]),
+    "vq_gather_st_loss_scatter_noalloc": (_i, [_p, _i, _i64, _i, _i64, _p, _p, _i, _p, _i64, _p, _p, _p, _i, _p, _p, _f, _p]),
     "vq_ema_update": (_i, [_p, _p, _p, _p, _p, _i, _i, _f, _f, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i, _p, _p]),
     "vq_backward": (_i, [_p, _p, _p, _i64, _i, _i64, _p, _f, _p, _i, _p]),
     "vq_codebook_grad": (_i, [_p, _i, _i, _p, _f, _p, _p]),

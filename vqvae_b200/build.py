@@ -23,7 +23,7 @@ LIB = os.path.join(HERE, "libvq_b200.so")
 OBJDIR = os.path.join(HERE, "build")
 STAMP = os.path.join(OBJDIR, ".build_stamp")
 SOURCES = ["vq_abi.cu", "vq_assign_tc.cu", "vq_assign_tc3.cu", "vq_assign_simt.cu", "vq_pass.cu", "vq_ema.cu",
-           "vq_layout.cu", "vq_knn.cu"]
+           "vq_layout.cu", "vq_knn.cu", "vq_noalloc.cu"]
 HEADERS = ["vq_common.cuh", "vq_assign_tc.cuh"]
 CC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
             "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
