@@ -379,8 +379,9 @@ def measure(ctx, key, args, steps, warmup, full=True, clocks=True):
         # the pairing the module runs: the search leaves the counting-sort inputs in ws, the pass group picks them up
         t_assign = time_kernel(lambda: ops.assign(z, Ec, Eb, nrm, "bf16", idx, None, ws, presort=True, ws_clean=True),
                                it, ctx.flush)
+        idx64 = torch.empty(N, dtype=torch.int64, device=dev)
         t_pass = time_kernel(lambda: ops.gather_st_loss_scatter(z, idx, Ec, q, sq, ccnt, csum, VQ_STAT_SUM_Z, False, ws,
-                                                                presorted=True), it, ctx.flush)
+                                                                idx64_out=idx64, presorted=True), it, ctx.flush)
         flops = 2.0 * N * K * D                                   # 2*K*D per vector
         pass_bytes = N * (D * 2 + 4 + D * 2) + K * D * 4 * 2 + K * 4   # read z + idx, write q; codebook + stats once
         tf = flops / (t_assign * 1e-3) / 1e12
@@ -392,7 +393,7 @@ def measure(ctx, key, args, steps, warmup, full=True, clocks=True):
                            "algorithmic_bytes": N * (D * 2 + 4) + K * D * 2 + K * 4,
                            "peak_source": peaks["src"] + " burst (kernel timed alone)", "ms_per_launch": t_assign}
         rec["roofline_pass"] = {"kernel": "scatter_ranked_kernel + pass_kernel (a-2..a-5; histogram / ranks / scan come "
-                                          "from the search kernel)", "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"],
+                                          "from the search kernel; the scatter also widens the indices to int64)", "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"],
                                 "unit": "GB/s", "frac": gbs / peaks["hbm"], "traffic": load_traffic(key, "pass_group"),
                                 "traffic_source": TRAFFIC_SOURCE, "algorithmic_bytes": pass_bytes,
                                 "peak_source": peaks["src"], "ms_per_launch": t_pass}
@@ -487,7 +488,7 @@ def run_native(args):
     if ctx.world > 1:
         from vqvae_b200 import parallel
         dp = {"replicas_identical": False, "rows_counted": None, "rows_expected": None, "exchange": mod.peer_exchange
-              if mod._peers is None else "peer"}
+              if mod._peers is None else "peer (" + mod._peers.kind + ")", "exchange_timing_us": mod.peer_exchange_timing()}
         try:
             parallel.assert_replicas_identical(mod.codebook)
             dp["replicas_identical"] = True

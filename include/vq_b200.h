@@ -35,7 +35,7 @@ extern "C" {
 typedef struct CUstream_st* vq_stream_t; /* == cudaStream_t */
 #endif
 
-#define VQ_ABI_VERSION 3
+#define VQ_ABI_VERSION 4
 
 enum { VQ_OK = 0, VQ_ERR_ARG = 1, VQ_ERR_CUDA = 2, VQ_ERR_UNSUPPORTED = 3 };
 /* storage type of latents and quantised rows.  fp16 is the reference script's DEFAULT autocast dtype
@@ -101,7 +101,7 @@ int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const 
               vq_stream_t stream);
 
 /* a-2..a-5 in ONE pass over z: q_out[n] = E_f32[idx[n]] (cast to out_dtype == in_dtype), sq_err_sum[0] =
- * sum (z - q)^2 (fp32, over finite rows), and -- when code_cnt/code_sum are non-NULL -- cnt_k and the per-code
+ * sum (z - q)^2 (fp32, over finite rows; q_out may be NULL: loss and statistics only, see vq_gather_rows_cf), and -- when code_cnt/code_sum are non-NULL -- cnt_k and the per-code
  * sums selected by stat_kind.  Rows are visited in code-sorted order (a counting sort of idx built in ws),
  * so the sums are segmented reductions in registers with one vector red per (code, 64-row slice).
  * deterministic != 0 makes the visiting order, hence every fp32 sum, run-to-run reproducible.
@@ -146,14 +146,18 @@ int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* cod
  * HOST arrays of `world` DEVICE pointers (entry `rank` = this rank's own buffers, the others opened with vq_ipc_open);
  * each flag array holds VQ_MAX_PEERS int32, zero-initialised; `epoch` must increase by one per call on every rank
  * (start at 1).  The caller alternates between two statistics buffers from step to step (a rank may still be reading
- * the previous step's buffer of a faster peer).  The reference has no distributed code: SURVEY.md 8(e). */
+ * the previous step's buffer of a faster peer).  mc_stats (nullable): the MULTICAST (NVLS) address that maps this step's
+ * statistics buffer of all `world` ranks (cuMulticast* / torch symmetric memory): the kernels then fetch every element
+ * with one multimem.ld_reduce -- the sum over ranks is formed inside the NVSwitch, one NVLink read per element instead of
+ * `world` -- and peer_stats is used for nothing but the flags' companions.  The reference has no distributed code:
+ * SURVEY.md 8(e). */
 #define VQ_MAX_PEERS 16
 #define VQ_IPC_HANDLE_BYTES 64
 int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D, float decay, float eps, int do_ema,
                      int search, void* E_bf16, float* e_norm2, int64_t* usage_total, int32_t* steps_since_used,
                      float* perplexity /* [1] */, int32_t* n_dead /* [1] */, int dead_after, int update_usage, void* ws,
                      const void* const* peer_stats /* host [world] */, void* const* peer_flags /* host [world] */,
-                     int world, int rank, int epoch, vq_stream_t stream);
+                     int world, int rank, int epoch, const void* mc_stats /* nullable */, vq_stream_t stream);
 /* Bound of the cross-rank wait inside vq_ema_update_dp, in milliseconds of wall-clock time (default 1 800 000 = 30 min;
  * <= 0 waits for ever); returns the previous value.  It is a rendezvous of processes -- a rank may be late by seconds or
  * minutes (rank-0-only validation, checkpointing, a data-loader stall) -- so it is NOT the kernels' internal hang bound.
@@ -180,6 +184,14 @@ int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_s
 /* a-0 layout ingest: batched transpose src [B, R, C] -> dst [B, C, R] (dense, dtype VQ_DT_*).  Channel-first latents
  * [B, D, S] (frl/models/representation.py:317-334) -> rows [B*S, D]: R = D, C = S; quantised rows back: R = S, C = D. */
 int vq_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, vq_stream_t stream);
+
+/* a-2 for channel-first callers: q_cf[b, d, s] = E_f32[idx[b*S + s]][d] cast to `dtype`, i.e. the
+ * quantised output written straight in the live model's [B, D, *spatial] layout (frl/models/representation.py:317-334)
+ * from the indices alone -- no row-major q and no transpose-out pass.  Pair it with vq_gather_st_loss_scatter(q_out = NULL):
+ * the pass then only reads the latent rows (loss + statistics).  idx must be final (after the pass canonicalised
+ * non-finite rows to 0). */
+int vq_gather_rows_cf(const int32_t* idx, const float* E_f32, int K, int D, int64_t B, int64_t S, void* q_cf, int dtype,
+                      vq_stream_t stream);
 
 /* SURVEY.md 8(f) row 4 -- mutual-kNN pair mining of the live training step (frl/losses/pairs.py:531-610
  * `pairs_mutual_knn_chunked`; call site frl/training/representation/step.py:734-741), the top-k generalisation of the

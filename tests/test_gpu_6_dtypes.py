@@ -191,3 +191,43 @@ def test_module_on_non_current_device():
     with pytest.raises(RuntimeError, match="different devices"):
         from vqvae_b200 import ops
         ops.layout_transpose(torch.zeros(1, 8, 8, device="cuda:0"), torch.zeros(1, 8, 8, device="cuda:1"))
+
+
+# ------------------------------------------------------------------------------------------------ channel-first (8f row 3)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("B,D,spatial", [(3, 64, (16, 16)), (2, 128, (5, 9, 7)), (1, 40, (33,)), (4, 256, (8, 8))])
+def test_channel_first_call_no_transpose_out(B, D, spatial, dtype):
+    """[B, D, *spatial] in and out (frl/models/representation.py:317-334): q comes straight from vq_gather_rows_cf, the
+    pass is read-only, the backward is elementwise on the channel-first tensors.  Must equal the channel-last call on the
+    permuted tensor: indices and q bit-equal, loss / gradients / codebook to the dtype's tolerance."""
+    from vqvae_b200 import VectorQuantizer
+    torch.manual_seed(D + len(spatial))
+    K = 96
+    a = VectorQuantizer(D, K, quantizer="ema", channel_first=True, deterministic=True, cuda_graph=False).cuda().train()
+    b = VectorQuantizer(D, K, quantizer="ema", channel_first=False, deterministic=True, cuda_graph=False).cuda().train()
+    b.load_state_dict(a.state_dict())
+    z = torch.randn(B, D, *spatial, device="cuda").to(dtype)
+    w = torch.randn(B, D, *spatial, device="cuda").to(dtype)
+    za = z.clone().requires_grad_(True)
+    perm = (0,) + tuple(range(2, z.dim())) + (1,)
+    inv = (0, z.dim() - 1) + tuple(range(1, z.dim() - 1))
+    zb = z.permute(*perm).contiguous().requires_grad_(True)
+    qa, la, ia = a(za)
+    qb, lb, ib = b(zb)
+    assert qa.shape == z.shape and ia.shape == (B, *spatial) and qa.dtype == dtype
+    assert torch.equal(ia, ib)
+    assert torch.equal(qa, qb.permute(*inv))
+    tol = 1e-5 if dtype == torch.float32 else 1e-3
+    assert abs(float(la) - float(lb)) <= tol * abs(float(lb))
+    ((qa * w).float().sum() + 3.0 * la).backward()
+    ((qb * w.permute(*perm)).float().sum() + 3.0 * lb).backward()
+    assert torch.allclose(za.grad.float(), zb.grad.permute(*inv).float(), rtol=tol, atol=tol)
+    assert torch.allclose(a.codebook, b.codebook, rtol=tol, atol=1e-6)
+    # the forward launches ONE layout pass (transpose in), none out
+    from torch.profiler import ProfilerActivity, profile
+    with torch.no_grad():
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            a(z)
+            torch.cuda.synchronize()
+    names = [e.name for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+    assert sum("transpose_kernel" in n for n in names) == 1 and sum("gather_rows_cf_kernel" in n for n in names) == 1

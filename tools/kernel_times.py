@@ -37,6 +37,7 @@ ap.add_argument("--exchange", default="auto")
 ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp16", "fp32"])
 ap.add_argument("--search", default="auto")
 ap.add_argument("--json", default=None)
+ap.add_argument("--cf", type=int, default=0, help="channel-first call: latents as [N / S, D, S] with S = this value (e.g. 1024)")
 args = ap.parse_args()
 
 world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -56,7 +57,9 @@ N, K, D = wl["N"], wl["K"], wl["D"]
 dt = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}[args.dtype]
 z, E = make_inputs(wl, rank, dev, dtype=dt, data=args.data)
 mod = VectorQuantizer(D, K, quantizer="ema", peer_exchange=args.exchange, deterministic=args.mode == "det",
-                      search=args.search).to(dev).train()
+                      search=args.search, channel_first=args.cf > 0).to(dev).train()
+if args.cf > 0:
+    z = z.view(N // args.cf, args.cf, D).transpose(1, 2).contiguous()          # [B, D, S]
 with torch.no_grad():
     mod.codebook.copy_(E); mod.ema_sum.copy_(E)
 
@@ -93,6 +96,8 @@ if world > 1:
     dist.barrier()
 from torch.profiler import ProfilerActivity, profile  # noqa: E402
 
+mod.peer_exchange_timing(reset=True)
+
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(args.steps):
         step()
@@ -125,7 +130,8 @@ tl = []
 if len(starts) >= 2:
     a, b = starts[-2], starts[-1]
     tl = [(short(e.name), e.time_range.start, e.time_range.end) for e in evs[a:b]]
-out = {"rank": rank, "table": table, "timeline": tl}
+out = {"rank": rank, "table": table, "timeline": tl, "peer_timing": mod.peer_exchange_timing(),
+       "exchange": None if mod._peers is None else mod._peers.kind}
 if world > 1:
     allout = [None] * world
     dist.all_gather_object(allout, out)
@@ -139,6 +145,9 @@ if rank == 0:
         step_us += v["mean_us"] * v["n"] / args.steps
     print(f"sum of kernel time per step: {step_us:.1f} us")
     if world > 1:
+        print("# exchange:", allout[0]["exchange"])
+        print("# in-kernel timing of the fused exchange per rank, mean over the profiled steps (wait for the last peer's signal / sum the count vectors):",
+              [(o["rank"], o["peer_timing"]) for o in allout])
         t0 = min(t[1] for o in allout for t in o["timeline"])
         print("# timeline of one step: rank, kernel, start us, end us (relative to the earliest start over ranks)")
         for o in allout:

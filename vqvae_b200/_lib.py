@@ -21,7 +21,7 @@ VQ_STAT_ACCUMULATE = 16
 VQ_STAT_PRESORTED = 32      # idx comes from vq_assign(... | VQ_SEARCH_PRESORT) on the same workspace
 VQ_SEARCH_WS_CLEAN = 512    # caller vouches that the workspace counters are zero (see include/vq_b200.h)
 VQ_SEARCH_PRESORT = 256     # vq_assign also leaves histogram / ranks / scan of idx in the workspace
-ABI_VERSION = 3
+ABI_VERSION = 4
 MAX_PEERS, IPC_HANDLE_BYTES = 16, 64
 NOALLOC_SCRATCH_BYTES = 4 << 20
 
@@ -46,9 +46,10 @@ SIGNATURES = {
     "vq_backward": (_i, [_p, _p, _p, _i64, _i, _i64, _p, _f, _p, _i, _p]),
     "vq_codebook_grad": (_i, [_p, _i, _i, _p, _f, _p, _p]),
     "vq_cast_bf16": (_i, [_p, _i64, _i, _i64, _p, _p]),
+    "vq_gather_rows_cf": (_i, [_p, _p, _i, _i, _i64, _i64, _p, _i, _p]),
     "vq_layout_transpose": (_i, [_p, _p, _i64, _i64, _i64, _i, _p]),
     "vq_ema_update_dp": (_i, [_p, _p, _p, _i, _i, _f, _f, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i, _p,
-                              C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _i, _i, _i, _p]),
+                              C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _i, _i, _i, _p, _p]),
     "vq_ipc_alloc": (_i, [C.c_size_t, C.POINTER(C.c_void_p), _p]),
     "vq_ipc_free": (_i, [_p]),
     "vq_ipc_open": (_i, [_p, C.POINTER(C.c_void_p)]),

@@ -63,7 +63,7 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                       int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
                       int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
                       int dead_after, int update_usage, void* ws, cudaStream_t st, const void* const* peer_stats,
-                      void* const* peer_flags, int world, int rank, int epoch);
+                      void* const* peer_flags, int world, int rank, int epoch, const void* mc_stats);
 int launch_backward(const void* z, const void* q, const void* gq, int64_t N, int D, int64_t ldz,
                     const float* grad_loss, float coef, void* gz, int dtype, cudaStream_t st);
 int launch_codebook_grad(const float* resid, int K, int D, const float* grad_loss, float coef, float* gE,
@@ -118,7 +118,7 @@ int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf
                "VQ_SEARCH_BF16 / VQ_SEARCH_F16");
     return launch_ema_update(const_cast<float*>(E_f32), nullptr, nullptr, nullptr, nullptr, K, D, 0.f, 0.f, 0, search,
                              E_bf16, e_norm2, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, stream, nullptr, nullptr,
-                             0, 0, 0);
+                             0, 0, 0, nullptr);
 }
 
 int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32, const void* E_bf16,
@@ -196,8 +196,9 @@ int vq_gather_st_loss_scatter(const void* z, int in_dtype, int64_t N, int D, int
         const int base_kind = stat_kind & ~(VQ_STAT_ACCUMULATE | VQ_STAT_PRESORTED);
         VQ_REQUIRE(base_kind == VQ_STAT_SUM_Z || base_kind == VQ_STAT_SUM_RESID, "bad stat_kind %d", stat_kind);
     }
-    VQ_REQUIRE(E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (idx != nullptr && z != nullptr && q_out != nullptr)),
+    VQ_REQUIRE(E_f32 != nullptr && sq_err_sum != nullptr && (N == 0 || (idx != nullptr && z != nullptr)),
                "vq_gather_st_loss_scatter: NULL argument");
+    if (q_out == nullptr) ldq = ldq < D ? D : ldq;     // q_out NULL: loss and statistics only (vq_gather_rows_cf writes q)
     const PassExtra extra{idx64_out, loss_out, loss_scale, 0};
     return launch_gather_pass(z, in_dtype, N, D, ldz, idx, E_f32, K, q_out, ldq, sq_err_sum, code_cnt, code_sum,
                               stat_kind, deterministic, extra, ws, stream);
@@ -211,19 +212,19 @@ int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* cod
     VQ_REQUIRE(search_ok(search), "vq_ema_update: bad search mode %d", search);
     return launch_ema_update(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, do_ema, search, E_bf16,
                              e_norm2, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws,
-                             stream, nullptr, nullptr, 0, 0, 0);
+                             stream, nullptr, nullptr, 0, 0, 0, nullptr);
 }
 
 int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D, float decay, float eps, int do_ema,
                      int search, void* E_bf16, float* e_norm2, int64_t* usage_total, int32_t* steps_since_used,
                      float* perplexity, int32_t* n_dead, int dead_after, int update_usage, void* ws,
                      const void* const* peer_stats, void* const* peer_flags, int world, int rank, int epoch,
-                     vq_stream_t stream) {
+                     const void* mc_stats, vq_stream_t stream) {
     VQ_REQUIRE(peer_stats != nullptr && peer_flags != nullptr, "vq_ema_update_dp: peer arrays are NULL");
     VQ_REQUIRE(search_ok(search), "vq_ema_update_dp: bad search mode %d", search);
     return launch_ema_update(E_f32, ema_cnt, ema_sum, nullptr, nullptr, K, D, decay, eps, do_ema, search, E_bf16, e_norm2,
                              usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws, stream,
-                             peer_stats, peer_flags, world, rank, epoch);
+                             peer_stats, peer_flags, world, rank, epoch, mc_stats);
 }
 
 int vq_knn_workspace_bytes(int64_t N, int C, size_t* out_bytes) {
@@ -291,6 +292,15 @@ int vq_codebook_grad(const float* resid_sum, int K, int D, const float* grad_los
 int vq_cast_bf16(const float* src, int64_t N, int D, int64_t ld, void* dst, vq_stream_t stream) {
     VQ_REQUIRE(N == 0 || (src != nullptr && dst != nullptr), "vq_cast_bf16: NULL argument");
     return launch_cast_bf16(src, VQ_DT_F32, N, D, ld, dst, stream);
+}
+
+int vq_gather_rows_cf(const int32_t* idx, const float* E_f32, int K, int D, int64_t B, int64_t S, void* q_cf, int dtype,
+                      vq_stream_t stream) {
+    VQ_REQUIRE(dtype_ok(dtype), "vq_gather_rows_cf: bad dtype %d", dtype);
+    VQ_REQUIRE(B >= 0 && S >= 0 && D > 0 && K > 0, "vq_gather_rows_cf: bad shape B=%lld S=%lld D=%d K=%d", (long long)B,
+               (long long)S, D, K);
+    VQ_REQUIRE(B == 0 || S == 0 || (idx != nullptr && E_f32 != nullptr && q_cf != nullptr), "vq_gather_rows_cf: NULL argument");
+    return launch_gather_rows_cf(idx, E_f32, K, D, B, S, q_cf, dtype, stream);
 }
 
 int vq_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, vq_stream_t stream) {

@@ -57,6 +57,8 @@ int launch_assign_simt(const void* z, int in_dtype, int64_t N, int D, int64_t ld
                        const float* e_norm2, int K, int32_t* idx, float* smin, Presort ps, cudaStream_t st);
 int launch_cast_bf16(const void* src, int in_dtype, int64_t N, int D, int64_t ld, void* dst, cudaStream_t st);
 int launch_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, cudaStream_t st);
+int launch_gather_rows_cf(const int32_t* idx, const float* E_f32, int K, int D, int64_t B, int64_t S, void* q_cf, int dtype,
+                          cudaStream_t st);
 size_t knn_workspace_bytes(int64_t N, int C);
 int launch_knn_topk(const float* X, int64_t N, int C, const float* coords, const int32_t* patch, float pos_min_spatial,
                     int k, int64_t* knn_idx, float* knn_d2, void* ws, cudaStream_t st);

@@ -14,7 +14,9 @@ namespace {
 
 struct Scal {          // lives at offset 0 of the workspace
     float tot_new;     // sum_k n_k after the decay step
-    float pad[3];
+    float wait_us;     // peer exchange, SUM over steps: time between this rank's own signal and the last peer's signal
+    float read_us;     //   ... and reading + adding the W count vectors over NVLink (diagnostics: tools/kernel_times.py)
+    float n_steps;     //   ... steps summed (the host zeroes the three to start a measurement)
 };
 
 // ---- a-6 fused into a-7: peer-memory exchange ---------------------------------------------------------------
@@ -25,6 +27,9 @@ struct Scal {          // lives at offset 0 of the workspace
 struct Peers {
     const float* stats[VQ_MAX_PEERS];   // rank r's statistics buffer of this step (own buffer included)
     int32_t* flags[VQ_MAX_PEERS];       // rank r's flag array [VQ_MAX_PEERS]; slot s = last epoch signalled by rank s
+    const float* mc;                    // multicast (NVLS) address of this step's statistics buffer over all ranks, or NULL:
+                                        // one multimem.ld_reduce returns the SUM over ranks, added inside the NVSwitch --
+                                        // one NVLink read per element instead of W
     int world, rank, epoch;
     long long timeout_ns;               // cross-rank wait bound (vq_set_peer_timeout_ms); <= 0: wait for ever
 };
@@ -36,6 +41,18 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 __device__ __forceinline__ float ld_peer(const float* p) {
     float v;
     asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+// sum over all ranks of 4 consecutive floats / one float of the multicast-mapped statistics buffer (reduced in the switch)
+__device__ __forceinline__ float4 ld_reduce_v4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_reduce_f32(const float* mc) {
+    float v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc) : "memory");
     return v;
 }
 __device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
@@ -101,11 +118,24 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
     const float omg = 1.0f - decay;
     double s_n = 0.0, s_c = 0.0;
     int dead = 0;
+    unsigned long long tp0 = 0, tp1 = 0;
     if (kPeer) {
+        if (t == 0) tp0 = globaltimer_ns();
         peers_signal_and_wait(P);
+        if (t == 0) tp1 = globaltimer_ns();
         // all ranks' values of a batch are requested before the first is used (one NVLink round trip per batch, not one
         // per rank); the adds then run in rank order, so every rank forms bit-identical sums
         constexpr int KB = 4;
+        if (P.mc != nullptr) {                    // in-switch sum: one request per 4 codes (K_pad % 4 == 0 by layout)
+            for (int k4 = t * 4; k4 < K; k4 += 4096) {
+                if (k4 + 4 <= K) {
+                    const float4 c = ld_reduce_v4(P.mc + KD + k4);
+                    cnt_red[k4] = c.x; cnt_red[k4 + 1] = c.y; cnt_red[k4 + 2] = c.z; cnt_red[k4 + 3] = c.w;
+                } else {
+                    for (int k = k4; k < K; ++k) cnt_red[k] = ld_reduce_f32(P.mc + KD + k);
+                }
+            }
+        } else
         for (int k0 = t; k0 < K; k0 += 1024 * KB) {
             float v[KB][VQ_MAX_PEERS];
 #pragma unroll
@@ -124,6 +154,11 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
         }
         __syncthreads();
         code_cnt = cnt_red;
+        if (t == 0) {
+            scal->wait_us += (float)(tp1 - tp0) * 1e-3f;
+            scal->read_us += (float)(globaltimer_ns() - tp1) * 1e-3f;
+            scal->n_steps += 1.f;
+        }
     }
     for (int k = t; k < K; k += 1024) {
         const float c = code_cnt[k];
@@ -256,9 +291,26 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
     }
     float nrm = 0.f;
     constexpr int DB = 4;                     // elements per lane whose peer loads are in flight together
+    extern __shared__ float mc_row[];         // multicast path: [8 warps][D] rank-summed rows
+    const bool use_mc = kPeer && do_ema && P.mc != nullptr;
+    float* my_row = mc_row + (threadIdx.x >> 5) * D;
+    if (use_mc) {
+        // in-switch reduction: every lane asks for 16 bytes of the row's sum over ranks (all requests of the row are in
+        // flight together: one NVLink round trip per row, one read per element instead of W)
+        const float* src = P.mc + (int64_t)k * D;
+        if ((D & 3) == 0) {
+            for (int d4 = lane * 4; d4 < D; d4 += 128) *reinterpret_cast<float4*>(my_row + d4) = ld_reduce_v4(src + d4);
+        } else {
+            for (int d = lane; d < D; d += 32) my_row[d] = ld_reduce_f32(src + d);
+        }
+        __syncwarp();
+    }
     for (int d0 = lane; d0 < D; d0 += 32 * DB) {
         float cs[DB];
-        if (do_ema && kPeer) {                // one NVLink round trip for DB x world values, adds in rank order
+        if (use_mc) {
+#pragma unroll
+            for (int b = 0; b < DB; ++b) cs[b] = d0 + 32 * b < D ? my_row[d0 + 32 * b] : 0.f;
+        } else if (do_ema && kPeer) {         // one NVLink round trip for DB x world values, adds in rank order
             float v[DB][VQ_MAX_PEERS];
 #pragma unroll
             for (int b = 0; b < DB; ++b)
@@ -339,9 +391,10 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                       int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
                       int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
                       int dead_after, int update_usage, void* ws, cudaStream_t st, const void* const* peer_stats,
-                      void* const* peer_flags, int world, int rank, int epoch) {
+                      void* const* peer_flags, int world, int rank, int epoch, const void* mc_stats) {
     Peers P;
     P.world = 0; P.rank = 0; P.epoch = 0; P.timeout_ns = peer_timeout_ns();
+    P.mc = static_cast<const float*>(mc_stats);
     const bool peer = peer_stats != nullptr;
     if (peer) {
         VQ_REQUIRE(world >= 1 && world <= VQ_MAX_PEERS && rank >= 0 && rank < world && peer_flags != nullptr && epoch > 0,
@@ -381,8 +434,10 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
     }
     const int ne = round_up(K, 256);                 // codes incl. padding; vq_norm_elems(K) floats = ne norms + aug image
     const float k_eps = (float)((double)K * (double)eps);
+    const size_t apply_smem = (peer && do_ema && P.mc != nullptr) ? (size_t)8 * D * sizeof(float) : 0;
+    VQ_REQUIRE(apply_smem <= 48 * 1024, "vq_ema_update_dp: D=%d too large for the multicast path (D <= 1536)", D);
     VQ_CHECK_CUDA(launch_pdl(PDL_APPLY, (peer && do_ema) ? ema_apply_kernel<true> : ema_apply_kernel<false>, dim3((ne + 7) / 8),
-                             dim3(256), 0, st, E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, k_eps, do_ema,
+                             dim3(256), apply_smem, st, E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, k_eps, do_ema,
                              search, static_cast<const Scal*>(scal), static_cast<__nv_bfloat16*>(E_bf16), e_norm2, ne, P));
     VQ_CHECK_CUDA(cudaGetLastError());
     count_launch();

@@ -2,6 +2,8 @@
 // (the live model's layout, frl/models/representation.py:317-334) become the [N, D] rows the quantiser takes, and
 // the quantised rows go back to channel-first.  One pass, 64 x 64 tiles through shared memory, 4- or 8-byte
 // accesses coalesced on both sides.  HBM-bound: 2 * B*R*C*s bytes.   Definition: SURVEY.md 8(a-0), 8f row 3.
+#include <cuda_fp16.h>
+
 #include "vq_common.cuh"
 
 namespace vq {
@@ -85,7 +87,75 @@ int launch_t(const void* src, void* dst, int64_t B, int64_t R, int64_t C, cudaSt
     return VQ_OK;
 }
 
+// q_cf[b, d, s] = E[idx[b * S + s]][d] cast to the latent dtype: the quantised output written STRAIGHT in the live model's
+// channel-first layout [B, D, *spatial] (frl/models/representation.py:317-334) from the indices alone -- no row-major q,
+// no transpose-out pass.  One block per (b, 64 consecutive s): the 64 code rows come from the L2-resident fp32 master
+// (coalesced along d), are converted and parked in shared memory [d][s], and leave as 128-byte (64 x 2 B) or 256-byte
+// segments along s.  HBM traffic: N*D*s bytes written + 4 N read.
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+constexpr int GS = 64;        // s positions per block
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_rows_cf_kernel(const int32_t* __restrict__ idx, const float* __restrict__ E, int K, int D, int64_t S, int tiles_s,
+                      T* __restrict__ q) {
+    extern __shared__ unsigned char gsm[];
+    T* tile = reinterpret_cast<T*>(gsm);                   // [D][GS + 2]
+    __shared__ int codes[GS];
+    const int64_t b = blockIdx.x / tiles_s;
+    const int64_t s0 = (int64_t)(blockIdx.x % tiles_s) * GS;
+    const int ns = (int)(S - s0 < GS ? S - s0 : GS);
+    if (threadIdx.x < GS) {
+        int c = threadIdx.x < ns ? idx[b * S + s0 + threadIdx.x] : 0;
+        if ((unsigned)c >= (unsigned)K) c = 0;
+        codes[threadIdx.x] = c;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int LD = GS + 2;
+    for (int r = warp; r < ns; r += 8) {                   // a warp copies one code row, coalesced along d
+        const float* e = E + (int64_t)codes[r] * D;
+        for (int d = lane; d < D; d += 32) tile[d * LD + r] = from_f32<T>(__ldg(e + d));
+    }
+    __syncthreads();
+    T* out = q + b * D * S + s0;
+    for (int i = threadIdx.x; i < D * GS; i += 256) {      // consecutive threads -> consecutive s of one d
+        const int d = i / GS, r = i % GS;
+        if (r < ns) out[(int64_t)d * S + r] = tile[d * LD + r];
+    }
+}
+
+template <typename T>
+int launch_gather_cf_t(const int32_t* idx, const float* E, int K, int D, int64_t B, int64_t S, void* q, cudaStream_t st) {
+    const int tiles_s = (int)ceil_div64(S, GS);
+    const int64_t blocks = B * tiles_s;
+    VQ_REQUIRE(blocks < (int64_t(1) << 31), "vq_gather_rows_cf: too many tiles");
+    const size_t smem = (size_t)D * (GS + 2) * sizeof(T);
+    VQ_REQUIRE(smem <= 200 * 1024, "vq_gather_rows_cf: D=%d too large", D);
+    static int attr_dev = -1;
+    const int cur = current_device();
+    if (attr_dev != cur) {
+        VQ_CHECK_CUDA(cudaFuncSetAttribute(gather_rows_cf_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_dev = cur;
+    }
+    gather_rows_cf_kernel<T><<<(unsigned)blocks, 256, smem, st>>>(idx, E, K, D, S, tiles_s, static_cast<T*>(q));
+    VQ_CHECK_CUDA(cudaGetLastError());
+    count_launch();
+    return VQ_OK;
+}
+
 }  // namespace
+
+int launch_gather_rows_cf(const int32_t* idx, const float* E_f32, int K, int D, int64_t B, int64_t S, void* q_cf, int dtype,
+                          cudaStream_t st) {
+    if (B == 0 || S == 0) return VQ_OK;
+    if (dtype == VQ_DT_F32) return launch_gather_cf_t<float>(idx, E_f32, K, D, B, S, q_cf, st);
+    if (dtype == VQ_DT_F16) return launch_gather_cf_t<__half>(idx, E_f32, K, D, B, S, q_cf, st);
+    return launch_gather_cf_t<__nv_bfloat16>(idx, E_f32, K, D, B, S, q_cf, st);
+}
 
 int launch_layout_transpose(const void* src, void* dst, int64_t B, int64_t R, int64_t C, int dtype, cudaStream_t st) {
     VQ_REQUIRE(B >= 0 && R >= 0 && C >= 0, "vq_layout_transpose: bad shape");

@@ -635,7 +635,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
                                 loss = fmaf(d, d, loss);
                                 acc[j][x] += (stat_kind & 15) == VQ_STAT_SUM_RESID ? d : zf[x];
                             }
-                            st_stream_16(q + (int64_t)r * ldq + v * EPV, qv[j]);
+                            if (q != nullptr) st_stream_16(q + (int64_t)r * ldq + v * EPV, qv[j]);
                         }
                     }
                     ++cnt;
@@ -649,7 +649,7 @@ pass_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int32_t* __r
                             float e0[EPV];
 #pragma unroll
                             for (int x = 0; x < EPV; ++x) e0[x] = __ldg(E + v * EPV + x);
-                            st_stream_16(q + (int64_t)r * ldq + v * EPV, IO::pack(e0));
+                            if (q != nullptr) st_stream_16(q + (int64_t)r * ldq + v * EPV, IO::pack(e0));
                         }
                     }
                     if (lg == 0) {
@@ -763,7 +763,7 @@ pass_generic_kernel(const T* __restrict__ z, int64_t N, int D, int64_t ldz, int3
         if (X.idx64 != nullptr && lane == 0) X.idx64[row] = c;
         for (int d = lane; d < D; d += 32) {
             const float ev = E[(int64_t)c * D + d];
-            q[row * ldq + d] = (T)ev;
+            if (q != nullptr) q[row * ldq + d] = (T)ev;
             if (!bad) {
                 const float zf = (float)z[row * ldz + d];
                 const float df = zf - ev;

@@ -175,12 +175,12 @@ def gather_st_loss_scatter(z: torch.Tensor, idx: torch.Tensor, E: torch.Tensor, 
         if presorted:
             stat_kind |= _lib.VQ_STAT_PRESORTED
         N, D, ld = _rows(z)
-        _, _, ldq = _rows(q_out)
+        ldq = _rows(q_out)[2] if q_out is not None else D        # q_out None: loss and statistics only (gather_rows_cf)
         K = E.shape[0]
-        assert q_out.dtype == z.dtype and q_out.shape == z.shape
+        assert q_out is None or (q_out.dtype == z.dtype and q_out.shape == z.shape)
         assert idx.dtype == torch.int32 and E.dtype == torch.float32 and E.is_contiguous()
         check(_lib.load().vq_gather_st_loss_scatter(_ptr(z), _dt(z), N, D, ld, _ptr(idx), _ptr(E), K, _ptr(q_out),
-                                                    _dt(q_out), ldq, _ptr(sq_err_sum), _ptr(code_cnt), _ptr(code_sum),
+                                                    _dt(z), ldq, _ptr(sq_err_sum), _ptr(code_cnt), _ptr(code_sum),
                                                     stat_kind, int(bool(deterministic)), _ptr(idx64_out), _ptr(loss_out),
                                                     float(loss_scale), _ptr(ws), on.stream),
               "vq_gather_st_loss_scatter")
@@ -230,6 +230,17 @@ def cast_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
         check(_lib.load().vq_cast_bf16(_ptr(src), N, D, ld, _ptr(dst), on.stream), "vq_cast_bf16")
 
 
+def gather_rows_cf(idx: torch.Tensor, E: torch.Tensor, q_cf: torch.Tensor) -> None:
+    """q_cf [B, D, S] (dense) <- E[idx[b * S + s]][d] cast to q_cf's dtype: the quantised output straight in channel-first
+    layout (include/vq_b200.h: vq_gather_rows_cf)."""
+    with _On(idx, E, q_cf) as on:
+        B, D, S = q_cf.shape
+        assert q_cf.is_contiguous() and idx.dtype == torch.int32 and idx.numel() >= B * S and idx.is_contiguous()
+        assert E.dtype == torch.float32 and E.is_contiguous() and E.shape[1] == D
+        check(_lib.load().vq_gather_rows_cf(_ptr(idx), _ptr(E), E.shape[0], D, B, S, _ptr(q_cf), _dt(q_cf), on.stream),
+              "vq_gather_rows_cf")
+
+
 def layout_transpose(src: torch.Tensor, dst: torch.Tensor) -> None:
     """src [B, R, C] -> dst [B, C, R], both dense (a-0: channel-first <-> row layout)."""
     with _On(src, dst) as on:
@@ -242,7 +253,7 @@ def ema_update_dp(E: torch.Tensor, ema_cnt: torch.Tensor, ema_sum: torch.Tensor,
                   do_ema: bool, search: str, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor,
                   usage_total: torch.Tensor, steps_since_used: torch.Tensor, perplexity: torch.Tensor,
                   n_dead: torch.Tensor, dead_after: int, update_usage: bool, ws: torch.Tensor, peer_stats, peer_flags,
-                  rank: int, epoch: int) -> None:
+                  rank: int, epoch: int, mc_stats: Optional[int] = None) -> None:
     """a-6 fused into a-7..a-9: the update kernels add every rank's statistics through peer memory
     (peer_stats / peer_flags: lists of `world` raw device pointers, own buffers at index `rank`)."""
     with _On(E, ema_cnt, ema_sum, E_bf16, e_norm2, usage_total, steps_since_used, perplexity, n_dead, ws) as on:
@@ -255,4 +266,4 @@ def ema_update_dp(E: torch.Tensor, ema_cnt: torch.Tensor, ema_sum: torch.Tensor,
                                            int(bool(do_ema)), SEARCH_MODES[search] & 3, _ptr(E_bf16), _ptr(e_norm2),
                                            _ptr(usage_total), _ptr(steps_since_used), _ptr(perplexity), _ptr(n_dead),
                                            int(dead_after), int(bool(update_usage)), _ptr(ws), ps, pf, world, int(rank),
-                                           int(epoch), on.stream), "vq_ema_update_dp")
+                                           int(epoch), mc_stats or None, on.stream), "vq_ema_update_dp")

@@ -85,6 +85,82 @@ class _RawCudaBuffer:
         self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
+class SymmExchange:
+    """Statistics exchange buffers on torch symmetric memory (plumbing only: allocation + rendezvous): same layout and
+    interface as PeerExchange -- [stats 0 | stats 1 | flags] per rank, peer pointers for the flags -- plus, where the
+    node has NVLS, the MULTICAST address of the allocation: the EMA kernels then read every statistic with one
+    multimem.ld_reduce (sum over ranks formed inside the NVSwitch, one NVLink read per element instead of W)."""
+
+    def __init__(self, numel: int, device: torch.device, group=None, timeout_s: Optional[float] = None):
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        lib = _lib.load()
+        if timeout_s is None:
+            timeout_s = float(os.environ.get("VQ_PEER_TIMEOUT_S", "1800"))
+        lib.vq_set_peer_timeout_ms(int(timeout_s * 1000))
+        self.group, self.numel, self.device = group, int(numel), device
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > _lib.MAX_PEERS:
+            raise RuntimeError(f"SymmExchange supports at most {_lib.MAX_PEERS} ranks")
+        stats_bytes = (self.numel * 4 + 255) // 256 * 256
+        self._stats_bytes = stats_bytes
+        total_f = (2 * stats_bytes + 256) // 4
+        g = group if group is not None else dist.group.WORLD
+        self._t = symm.empty(total_f, dtype=torch.float32, device=device)
+        self._h = symm.rendezvous(self._t, g.group_name)
+        self._t.zero_()
+        self._peer_base = [int(p) for p in self._h.buffer_ptrs]
+        mc = getattr(self._h, "multicast_ptr", 0) or 0
+        self._mc_base = int(mc) if os.environ.get("VQ_PEER_MULTICAST", "1") != "0" else 0
+        self.stats = [self._t[i * stats_bytes // 4: i * stats_bytes // 4 + self.numel] for i in range(2)]
+        self.epoch = 0
+        self.kind = "symm+multicast" if self._mc_base else "symm"
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)            # every allocation is zeroed and mapped before the first signal
+
+    def next_buffer(self) -> torch.Tensor:
+        self.epoch += 1
+        return self.stats[self.epoch & 1]
+
+    def peer_stats(self):
+        return [b + (self.epoch & 1) * self._stats_bytes for b in self._peer_base]
+
+    def peer_flags(self):
+        return [b + 2 * self._stats_bytes for b in self._peer_base]
+
+    def mc_stats(self):
+        return self._mc_base + (self.epoch & 1) * self._stats_bytes if self._mc_base else None
+
+    def close(self) -> None:
+        if self._t is None:
+            return
+        torch.cuda.synchronize()
+        if dist.is_initialized():
+            dist.barrier(group=self.group)
+        self._t, self._h, self.stats = None, None, []
+
+
+def make_exchange(numel: int, device: torch.device, group=None, timeout_s: Optional[float] = None):
+    """Symmetric-memory exchange (with the in-switch reduction where the node has NVLS) when torch provides it, else the
+    CUDA-IPC one.  VQ_PEER_SYMM=0 forces the IPC path.  Every rank takes the same branch (the choice is all-reduced)."""
+    ok = os.environ.get("VQ_PEER_SYMM", "1") != "0"
+    ex = None
+    if ok:
+        try:
+            ex = SymmExchange(numel, device, group, timeout_s)
+        except Exception as exc:          # no symmetric memory on this build / node: the IPC path does the same job
+            import warnings
+            warnings.warn(f"vqvae_b200: symmetric-memory exchange unavailable ({type(exc).__name__}: {exc}); using CUDA IPC")
+            ex = None
+    flag = torch.tensor([1 if ex is not None else 0], device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    if int(flag) == 1:
+        return ex
+    if ex is not None:
+        ex.close()
+    return PeerExchange(numel, device, group, timeout_s)
+
+
 class PeerExchange:
     """Peer-memory statistics exchange for the fused a-6 + a-7 update (one process per GPU, one node).
 
@@ -131,7 +207,11 @@ class PeerExchange:
         self.stats = [torch.as_tensor(_RawCudaBuffer(self._base + i * stats_bytes, self.numel, "<f4"), device=device)
                       for i in range(2)]
         self.epoch = 0
+        self.kind = "ipc"
         dist.barrier(group=group)            # every allocation is zeroed and mapped before the first signal
+
+    def mc_stats(self):
+        return None
 
     def next_buffer(self) -> torch.Tensor:
         """Statistics buffer the NEXT step writes (call once per step, before the pass kernel)."""

@@ -128,6 +128,44 @@ class _LayoutTranspose(torch.autograd.Function):
         return out
 
 
+class _VQFunctionCF(torch.autograd.Function):
+    """Channel-first call: z [B, D, S] -> (q [B, D, S], loss, idx [B*S]).  Backward = straight-through + commitment on the
+    channel-first tensors themselves (elementwise, so no layout pass), codebook gradient from the residual sums."""
+
+    @staticmethod
+    def forward(ctx, z3: torch.Tensor, codebook: torch.Tensor, mod: "VectorQuantizer", search: str):
+        B, D, S = z3.shape
+        rows = torch.empty((B, S, D), dtype=z3.dtype, device=z3.device)
+        ops.layout_transpose(z3, rows)                               # the ONE layout pass of the call
+        qcf = torch.empty_like(z3)
+        mod._ensure_shadow(search)
+        loss, idx, code_sum = mod._run_step_cf(rows.view(B * S, D), qcf, search)
+        ctx.save_for_backward(z3, qcf)
+        ctx.mod, ctx.n_rows = mod, B * S
+        ctx.resid = code_sum.clone() if (mod.quantizer == "st" and codebook.requires_grad) else None
+        ctx.mark_non_differentiable(idx)
+        return qcf, loss.reshape(()), idx
+
+    @staticmethod
+    def backward(ctx, grad_q, grad_loss, _grad_idx):
+        z3, qcf = ctx.saved_tensors
+        mod, N = ctx.mod, ctx.n_rows
+        B, D, S = z3.shape
+        dev = z3.device
+        gl = (torch.zeros(1, dtype=torch.float32, device=dev) if grad_loss is None
+              else grad_loss.detach().to(torch.float32).reshape(1))
+        grad_z = grad_E = None
+        if ctx.needs_input_grad[0]:
+            gq = None if grad_q is None else grad_q.to(z3.dtype).contiguous().view(B * D, S)
+            grad_z = torch.empty_like(z3)
+            ops.backward(z3.view(B * D, S), qcf.view(B * D, S), gq, gl, 2.0 * mod.beta / float(max(N * D, 1)),
+                         grad_z.view(B * D, S))
+        if ctx.needs_input_grad[1] and ctx.resid is not None:
+            grad_E = torch.empty((mod.codebook_size, D), dtype=torch.float32, device=dev)
+            ops.codebook_grad(ctx.resid, gl, 2.0 / float(max(N * D, 1)), grad_E)
+        return grad_z, grad_E, None, None
+
+
 class VectorQuantizer(nn.Module):
     """Nearest-codebook quantiser with straight-through output, commitment/codebook loss and (in "ema"
     mode) an EMA codebook update, all on hand-written sm_100a kernels.
@@ -313,18 +351,22 @@ class VectorQuantizer(nn.Module):
         import torch.distributed as dist
         world = dist.get_world_size(self.process_group)
         ok = dist.get_backend(self.process_group) == "nccl" and world <= int(os.environ.get("LOCAL_WORLD_SIZE", "1"))
-        if ok and self.peer_exchange == "auto":
-            # every rank reads all W buffers (one-shot): right for small statistics (latency-bound collective),
-            # wrong for large ones, where NCCL's bandwidth-optimal all-reduce moves 2 (W-1)/W of one buffer instead
-            ok = (self.codebook_size * (self.emb_dim + 1)) * 4 * world <= PEER_ONE_SHOT_MAX_BYTES
         if not ok:
             if self.peer_exchange == "peer":
                 raise RuntimeError("peer_exchange='peer' needs an NCCL process group whose ranks share one node")
             self.peer_exchange = "nccl"
             return False
         K, D = self.codebook_size, self.emb_dim
-        self._peers = parallel.PeerExchange(K * D + K, self.codebook.device, self.process_group,
-                                            timeout_s=self.peer_timeout_s)
+        ex = parallel.make_exchange(K * D + K, self.codebook.device, self.process_group, timeout_s=self.peer_timeout_s)
+        if self.peer_exchange == "auto" and ex.mc_stats() is None \
+                and (K * (D + 1)) * 4 * world > PEER_ONE_SHOT_MAX_BYTES:
+            # no in-switch reduction here, so every rank would read all W buffers (one-shot): right for small statistics
+            # (latency-bound collective), wrong for large ones, where NCCL's bandwidth-optimal all-reduce moves
+            # 2 (W-1)/W of one buffer instead.  With the multicast mapping each element crosses NVLink once: always fused.
+            ex.close()
+            self.peer_exchange = "nccl"
+            return False
+        self._peers = ex
         return True
 
     def _stats_buffer(self) -> torch.Tensor:
@@ -336,6 +378,19 @@ class VectorQuantizer(nn.Module):
             self._stats = torch.empty(K * D + K, dtype=torch.float32, device=dev)   # [code_sum | code_cnt]
         return self._stats
 
+    def peer_exchange_timing(self, reset: bool = False) -> Optional[dict]:
+        """Diagnostics of the fused peer exchange on this rank since the last reset (device -> host read): mean microseconds
+        per step between this rank's signal and the last peer's (the wait for the slowest rank) and spent adding the W
+        count vectors over NVLink.  reset=True restarts the averages."""
+        if self._peers is None or self._ws is None:
+            return None
+        v = self._ws[:16].view(torch.float32).cpu()
+        n = max(float(v[3]), 1.0)
+        out = {"steps": int(v[3]), "wait_us": float(v[1]) / n, "read_counts_us": float(v[2]) / n}
+        if reset:
+            self._ws[4:16].zero_()
+        return out
+
     def _dist_active(self) -> bool:
         return self.sync_stats and parallel.dist_active(self.process_group)
 
@@ -344,7 +399,7 @@ class VectorQuantizer(nn.Module):
         w = (1.0 + self.beta) if self.quantizer == "st" else self.beta
         return w / float(max(N * self.emb_dim, 1))
 
-    def _step_kernels(self, z2, q, idx32, idx64, sqerr, loss, search: str):
+    def _step_kernels(self, z2, q, idx32, idx64, sqerr, loss, search: str, q_cf=None):
         """a-1 .. a-9 on preallocated tensors; every launch goes to the current stream (capturable).  The int64 indices
         and the scaled loss are by-products of the gather pass: no torch arithmetic on the path."""
         N, D = z2.shape
@@ -355,10 +410,14 @@ class VectorQuantizer(nn.Module):
         E = self.codebook.detach()
         # the search leaves the counting-sort inputs of idx in ws, the pass picks them up (one scatter launch instead of
         # memset + histogram + scan/scatter)
-        ops.assign(z2, E, self._E_bf16, self._e_norm2, search, idx32, None, ws, presort=True, ws_clean=True)
         kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
+        # the search leaves the counting-sort inputs of idx in ws, the pass picks them up (one scatter launch instead of
+        # memset + histogram + scan/scatter)
+        ops.assign(z2, E, self._E_bf16, self._e_norm2, search, idx32, None, ws, presort=True, ws_clean=True)
         ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws,
                                    idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N), presorted=True)
+        if q_cf is not None:             # channel-first caller: q straight in [B, D, S] from the (final) indices, gathered
+            ops.gather_rows_cf(idx32, E, q_cf)   # from the codebook the search used -- before the EMA step rewrites it
         self._finish_step(code_cnt, code_sum, search, ws)
         return code_sum
 
@@ -366,6 +425,18 @@ class VectorQuantizer(nn.Module):
         return (self.cuda_graph and z2.shape[0] > 0 and z2.numel() * z2.element_size() <= GRAPH_MAX_BYTES
                 and not parallel.dist_active(self.process_group) and self._peers is None
                 and not torch.cuda.is_current_stream_capturing())
+
+    def _run_step_cf(self, z2, q_cf, search: str):
+        """Channel-first variant of _run_step: the pass only reads the rows (no row-major q), q_cf [B, D, S] is written by
+        the gather kernel.  -> (loss, idx int64, code_sum view)."""
+        N, D = z2.shape
+        dev = z2.device
+        idx32 = torch.empty(N, dtype=torch.int32, device=dev)
+        idx64 = torch.empty(N, dtype=torch.int64, device=dev)
+        sqerr = torch.empty(1, dtype=torch.float32, device=dev)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        code_sum = self._step_kernels(z2, None, idx32, idx64, sqerr, loss, search, q_cf=q_cf)
+        return loss, idx64, code_sum
 
     def _run_step(self, z2, search: str):
         """-> (q, sq_err_sum, idx int64, code_sum view).  Small single-process batches: first call with a given shape
@@ -449,7 +520,8 @@ class VectorQuantizer(nn.Module):
             px = self._peers
             ops.ema_update_dp(E, self.ema_cnt, self.ema_sum, self.ema_decay, self.ema_eps, True, search, self._E_bf16,
                               self._e_norm2, self.usage_total, self.steps_since_used, self.last_perplexity, self.n_dead,
-                              self.dead_after, True, ws, px.peer_stats(), px.peer_flags(), px.rank, px.epoch)
+                              self.dead_after, True, ws, px.peer_stats(), px.peer_flags(), px.rank, px.epoch,
+                              mc_stats=px.mc_stats())
             self._shadow_key = (E.data_ptr(), E._version, search)
             return
         if self._dist_active():
@@ -615,18 +687,21 @@ class VectorQuantizer(nn.Module):
         return q.reshape(*lead, D), loss.reshape(()), idx64.reshape(lead)
 
     def _forward_channel_first(self, z: torch.Tensor):
+        """[B, D, *spatial] in, quantized in the same layout out.  One transpose pass in (the search and the sorted pass
+        need row-major latents); NONE out: the pass only reads the rows and vq_gather_rows_cf writes q straight in
+        channel-first layout from the indices; the backward works on the channel-first tensors directly (elementwise)."""
         if z.dim() < 2 or z.shape[1] != self.emb_dim:
             raise ValueError(f"channel_first: dimension 1 is {tuple(z.shape)[1:2]}, expected emb_dim {self.emb_dim}")
         with torch.autocast(device_type="cuda", enabled=False):
             B, D, spatial = z.shape[0], z.shape[1], z.shape[2:]
-            in_dtype = z.dtype
             z3 = z.reshape(B, D, -1)
             search = self._search_for(z3.dtype)
+            in_dtype = z3.dtype
             if z3.dtype not in (torch.bfloat16, torch.float16, torch.float32):
                 z3 = z3.to(torch.float32)
-            rows = _LayoutTranspose.apply(z3)                          # [B, S, D]
-            q, loss, idx = _VQFunction.apply(rows.reshape(-1, D), self.codebook, self, search)
-            qcf = _LayoutTranspose.apply(q.reshape(B, -1, D))          # [B, D, S]
+            if not z3.is_contiguous():
+                z3 = z3.contiguous()
+            qcf, loss, idx = _VQFunctionCF.apply(z3, self.codebook, self, search)
             if qcf.dtype != in_dtype:
                 qcf = qcf.to(in_dtype)
             return qcf.reshape(B, D, *spatial), loss, idx.reshape(B, *spatial)
