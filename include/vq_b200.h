@@ -35,7 +35,7 @@ extern "C" {
 typedef struct CUstream_st* vq_stream_t; /* == cudaStream_t */
 #endif
 
-#define VQ_ABI_VERSION 4
+#define VQ_ABI_VERSION 5
 
 enum { VQ_OK = 0, VQ_ERR_ARG = 1, VQ_ERR_CUDA = 2, VQ_ERR_UNSUPPORTED = 3 };
 /* storage type of latents and quantised rows.  fp16 is the reference script's DEFAULT autocast dtype
@@ -149,15 +149,23 @@ int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* cod
  * the previous step's buffer of a faster peer).  mc_stats (nullable): the MULTICAST (NVLS) address that maps this step's
  * statistics buffer of all `world` ranks (cuMulticast* / torch symmetric memory): the kernels then fetch every element
  * with one multimem.ld_reduce -- the sum over ranks is formed inside the NVSwitch, one NVLink read per element instead of
- * `world` -- and peer_stats is used for nothing but the flags' companions.  The reference has no distributed code:
- * SURVEY.md 8(e). */
+ * `world` -- and peer_stats is used for nothing but the flags' companions.
+ * mc_reduced + reduced_local (nullable, together, with mc_stats; used when do_ema and K*D % 4 == 0): a second region of
+ * K*D floats at the same offset of every rank's allocation, given by its MULTICAST address and by this rank's own
+ * address.  The exchange then runs in two phases, whose NVLink traffic per GPU does not grow with `world`: rank r sums the
+ * r-th 1/world of the flat [K*D] array in the switch (multimem.ld_reduce) and writes it to every rank's region with
+ * multimem.st, a second flag round follows, and every rank applies the update from its own copy.  With it each flag array
+ * holds 2 * VQ_MAX_PEERS + 1 int32 (phase 1, phase 2, a block counter), zero-initialised.  Worth it for large codebooks
+ * (K*D of a few MB); for small ones the one-phase form has one kernel and one flag round less.
+ * The reference has no distributed code: SURVEY.md 8(e). */
 #define VQ_MAX_PEERS 16
 #define VQ_IPC_HANDLE_BYTES 64
 int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D, float decay, float eps, int do_ema,
                      int search, void* E_bf16, float* e_norm2, int64_t* usage_total, int32_t* steps_since_used,
                      float* perplexity /* [1] */, int32_t* n_dead /* [1] */, int dead_after, int update_usage, void* ws,
                      const void* const* peer_stats /* host [world] */, void* const* peer_flags /* host [world] */,
-                     int world, int rank, int epoch, const void* mc_stats /* nullable */, vq_stream_t stream);
+                     int world, int rank, int epoch, const void* mc_stats /* nullable */,
+                     void* mc_reduced /* nullable */, const void* reduced_local /* nullable */, vq_stream_t stream);
 /* Bound of the cross-rank wait inside vq_ema_update_dp, in milliseconds of wall-clock time (default 1 800 000 = 30 min;
  * <= 0 waits for ever); returns the previous value.  It is a rendezvous of processes -- a rank may be late by seconds or
  * minutes (rank-0-only validation, checkpointing, a data-loader stall) -- so it is NOT the kernels' internal hang bound.

@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/vq_b200.h but not exported"
     assert set(names) == set(_lib.SIGNATURES), "ctypes binding and header disagree"
-    assert lib.vq_abi_version() == _lib.ABI_VERSION == 4
+    assert lib.vq_abi_version() == _lib.ABI_VERSION == 5
 
 
 def test_host_only_entry_points():

@@ -140,7 +140,9 @@ for (N, K, D, dt) in CASES:
     flag = torch.tensor([1 if good else 0], device=dev)
     dist.broadcast(flag, src=0)
     ok &= bool(int(flag))
-    say(f"N={N} K={K} D={D} {dt}: DP vs oracle(concatenated) codebook rel err peer {worst['peer']:.2e} / nccl {worst['nccl']:.2e} "
+    kind = getattr(mods["peer"]._peers, "kind", None)
+    summary.setdefault("exchange_kinds", []).append(kind)
+    say(f"N={N} K={K} D={D} {dt} [peer exchange: {kind}]: DP vs oracle(concatenated) codebook rel err peer {worst['peer']:.2e} / nccl {worst['nccl']:.2e} "
         f"(tol {tol:g}), hard index mismatches {hard}, near ties {near}, loss rel err {loss_err}; peer-vs-nccl {err:.2e}, "
         f"usage equal {same_usage}, replicas bit-identical {identical}, rows {tot}/{expect} -> {'OK' if int(flag) else 'MISMATCH'}")
     for m in mods.values():

@@ -21,7 +21,7 @@ VQ_STAT_ACCUMULATE = 16
 VQ_STAT_PRESORTED = 32      # idx comes from vq_assign(... | VQ_SEARCH_PRESORT) on the same workspace
 VQ_SEARCH_WS_CLEAN = 512    # caller vouches that the workspace counters are zero (see include/vq_b200.h)
 VQ_SEARCH_PRESORT = 256     # vq_assign also leaves histogram / ranks / scan of idx in the workspace
-ABI_VERSION = 4
+ABI_VERSION = 5
 MAX_PEERS, IPC_HANDLE_BYTES = 16, 64
 NOALLOC_SCRATCH_BYTES = 4 << 20
 
@@ -49,7 +49,7 @@ SIGNATURES = {
     "vq_gather_rows_cf": (_i, [_p, _p, _i, _i, _i64, _i64, _p, _i, _p]),
     "vq_layout_transpose": (_i, [_p, _p, _i64, _i64, _i64, _i, _p]),
     "vq_ema_update_dp": (_i, [_p, _p, _p, _i, _i, _f, _f, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i, _p,
-                              C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _i, _i, _i, _p, _p]),
+                              C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _i, _i, _i, _p, _p, _p, _p]),
     "vq_ipc_alloc": (_i, [C.c_size_t, C.POINTER(C.c_void_p), _p]),
     "vq_ipc_free": (_i, [_p]),
     "vq_ipc_open": (_i, [_p, C.POINTER(C.c_void_p)]),

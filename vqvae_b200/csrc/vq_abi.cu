@@ -63,7 +63,8 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                       int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
                       int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
                       int dead_after, int update_usage, void* ws, cudaStream_t st, const void* const* peer_stats,
-                      void* const* peer_flags, int world, int rank, int epoch, const void* mc_stats);
+                      void* const* peer_flags, int world, int rank, int epoch, const void* mc_stats, void* mc_reduced,
+                      const void* reduced_local);
 int launch_backward(const void* z, const void* q, const void* gq, int64_t N, int D, int64_t ldz,
                     const float* grad_loss, float coef, void* gz, int dtype, cudaStream_t st);
 int launch_codebook_grad(const float* resid, int K, int D, const float* grad_loss, float coef, float* gE,
@@ -118,7 +119,7 @@ int vq_prepare_codebook(const float* E_f32, int K, int D, int search, void* E_bf
                "VQ_SEARCH_BF16 / VQ_SEARCH_F16");
     return launch_ema_update(const_cast<float*>(E_f32), nullptr, nullptr, nullptr, nullptr, K, D, 0.f, 0.f, 0, search,
                              E_bf16, e_norm2, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, stream, nullptr, nullptr,
-                             0, 0, 0, nullptr);
+                             0, 0, 0, nullptr, nullptr, nullptr);
 }
 
 int vq_assign(const void* z, int in_dtype, int64_t N, int D, int64_t ldz, const float* E_f32, const void* E_bf16,
@@ -212,19 +213,21 @@ int vq_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float* cod
     VQ_REQUIRE(search_ok(search), "vq_ema_update: bad search mode %d", search);
     return launch_ema_update(E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, do_ema, search, E_bf16,
                              e_norm2, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws,
-                             stream, nullptr, nullptr, 0, 0, 0, nullptr);
+                             stream, nullptr, nullptr, 0, 0, 0, nullptr, nullptr, nullptr);
 }
 
 int vq_ema_update_dp(float* E_f32, float* ema_cnt, float* ema_sum, int K, int D, float decay, float eps, int do_ema,
                      int search, void* E_bf16, float* e_norm2, int64_t* usage_total, int32_t* steps_since_used,
                      float* perplexity, int32_t* n_dead, int dead_after, int update_usage, void* ws,
                      const void* const* peer_stats, void* const* peer_flags, int world, int rank, int epoch,
-                     const void* mc_stats, vq_stream_t stream) {
+                     const void* mc_stats, void* mc_reduced, const void* reduced_local, vq_stream_t stream) {
     VQ_REQUIRE(peer_stats != nullptr && peer_flags != nullptr, "vq_ema_update_dp: peer arrays are NULL");
+    VQ_REQUIRE((mc_reduced == nullptr) == (reduced_local == nullptr) && (mc_reduced == nullptr || mc_stats != nullptr),
+               "vq_ema_update_dp: mc_reduced and reduced_local go together and need mc_stats");
     VQ_REQUIRE(search_ok(search), "vq_ema_update_dp: bad search mode %d", search);
     return launch_ema_update(E_f32, ema_cnt, ema_sum, nullptr, nullptr, K, D, decay, eps, do_ema, search, E_bf16, e_norm2,
                              usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, ws, stream,
-                             peer_stats, peer_flags, world, rank, epoch, mc_stats);
+                             peer_stats, peer_flags, world, rank, epoch, mc_stats, mc_reduced, reduced_local);
 }
 
 int vq_knn_workspace_bytes(int64_t N, int C, size_t* out_bytes) {

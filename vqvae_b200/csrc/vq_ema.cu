@@ -30,9 +30,15 @@ struct Peers {
     const float* mc;                    // multicast (NVLS) address of this step's statistics buffer over all ranks, or NULL:
                                         // one multimem.ld_reduce returns the SUM over ranks, added inside the NVSwitch --
                                         // one NVLink read per element instead of W
+    float* mc_red;                      // two-phase exchange (large K*D): multicast address of the [K*D] "reduced" region
+    const float* red;                   //   ... and this rank's own copy of it; NULL: every rank sums every element itself
     int world, rank, epoch;
     long long timeout_ns;               // cross-rank wait bound (vq_set_peer_timeout_ms); <= 0: wait for ever
 };
+// flag array of a rank (int32, zero-initialised by the caller): [0, MAX_PEERS) phase 1 "statistics of epoch e complete",
+// [MAX_PEERS, 2 MAX_PEERS) phase 2 "my slice of the reduced sums of epoch e is written everywhere", [2 MAX_PEERS] block
+// counter of ema_reduce_slice_kernel (returns to 0 at the end of every launch)
+constexpr int FLAG_PHASE2 = VQ_MAX_PEERS, FLAG_COUNTER = 2 * VQ_MAX_PEERS;
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -55,6 +61,11 @@ __device__ __forceinline__ float ld_reduce_f32(const float* mc) {
     asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc) : "memory");
     return v;
 }
+// one store that lands in EVERY rank's copy of the multicast-mapped region (replicated by the switch)
+__device__ __forceinline__ void st_multicast_v4(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
     asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -70,10 +81,10 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
 // vq_set_peer_timeout_ms to match the process group's timeout -- and unrelated to the mbarrier hang bound.  The poll
 // backs off to one system-scope load per ~2 us so that a long wait does not hammer NVLink.  A rank that is still
 // missing when the bound expires traps (the launch fails with a CUDA error, like a collective's watchdog would).
-__device__ __forceinline__ void peers_wait(const Peers& P) {
+__device__ __forceinline__ void peers_wait(const Peers& P, int phase_off = 0) {
     const int t = threadIdx.x;
     if (t < P.world) {
-        const int32_t* mine = P.flags[P.rank] + t;
+        const int32_t* mine = P.flags[P.rank] + phase_off + t;
         if (ld_acquire_sys(mine) < P.epoch) {
             const unsigned long long t0 = globaltimer_ns();
             unsigned ns = 32;
@@ -90,16 +101,66 @@ __device__ __forceinline__ void peers_wait(const Peers& P) {
     }
     __syncthreads();
 }
-__device__ __forceinline__ void peers_signal(const Peers& P) {      // threads 0 .. world-1
+__device__ __forceinline__ void peers_signal(const Peers& P, int phase_off = 0) {      // threads 0 .. world-1
     const int t = threadIdx.x;
     if (t < P.world) {
         __threadfence_system();
-        st_release_sys(P.flags[t] + P.rank, P.epoch);
+        st_release_sys(P.flags[t] + phase_off + P.rank, P.epoch);
     }
 }
 __device__ __forceinline__ void peers_signal_and_wait(const Peers& P) {
     peers_signal(P);
     peers_wait(P);
+}
+
+// Two-phase exchange for large codebooks (reduce-scatter -> all-gather inside the switch).  With one-phase reads every
+// rank pulls the whole [K*D] sum through the switch, so each GPU's NVLink carries W x K*D x 4 bytes outbound per step
+// (measured: ema_apply_kernel<true> 35 us at 2 GPUs, 55 us at 4, K=8192 D=256).  Here rank r reduces only the r-th 1/W of
+// the flat [K*D] array (multimem.ld_reduce: summed in the switch) and writes the result to EVERY rank's "reduced" region
+// with one multimem.st per 16 bytes (replicated by the switch): K*D x 4 bytes out and in per GPU whatever W is.  Every
+// rank then applies the EMA step from its own copy, which holds the same bits on all ranks.
+// First kernel of the update: block 0 signals phase 1, all blocks wait for it (polling this rank's own flag array), the
+// last block to finish signals phase 2.  ema_totals_kernel runs between this kernel and ema_apply_kernel, which hides the
+// phase-2 flag's flight time.
+__global__ void __launch_bounds__(256)
+ema_reduce_slice_kernel(int64_t KD4, const Peers P, Scal* __restrict__ scal) {
+    __shared__ int s_last;
+    pdl_wait();
+    pdl_trigger();
+    const int t = threadIdx.x;
+    unsigned long long tp0 = 0, tp1 = 0;
+    if (blockIdx.x == 0) {
+        if (t == 0) tp0 = globaltimer_ns();
+        peers_signal(P);
+    }
+    peers_wait(P);
+    if (blockIdx.x == 0 && t == 0) tp1 = globaltimer_ns();
+    const int64_t per = (KD4 + P.world - 1) / P.world;
+    const int64_t i0 = per * P.rank, i1 = i0 + per < KD4 ? i0 + per : KD4;
+    constexpr int U = 4;                                  // 16-byte requests in flight per thread
+    for (int64_t b = i0 + ((int64_t)blockIdx.x * U) * 256 + t; b < i1; b += (int64_t)gridDim.x * U * 256) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (b + u * 256 < i1) v[u] = ld_reduce_v4(P.mc + 4 * (b + u * 256));
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (b + u * 256 < i1) st_multicast_v4(P.mc_red + 4 * (b + u * 256), v[u]);
+    }
+    __threadfence_system();
+    __syncthreads();
+    int32_t* ctr = P.flags[P.rank] + FLAG_COUNTER;
+    if (t == 0) s_last = atomicAdd(ctr, 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (s_last) {
+        peers_signal(P, FLAG_PHASE2);
+        if (t == 0) *ctr = 0;
+    }
+    if (blockIdx.x == 0 && t == 0) {
+        scal->wait_us += (float)(tp1 - tp0) * 1e-3f;
+        scal->read_us += (float)(globaltimer_ns() - tp1) * 1e-3f;
+        scal->n_steps += 1.f;
+    }
 }
 
 // one block.  tot_new = sum_k (g n_k + (1-g) cnt_k) in a fixed order (double); usage / dead / perplexity.
@@ -120,8 +181,9 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
     int dead = 0;
     unsigned long long tp0 = 0, tp1 = 0;
     if (kPeer) {
+        const bool waited = P.red != nullptr;     // two-phase: ema_reduce_slice_kernel (earlier in the stream) did phase 1
         if (t == 0) tp0 = globaltimer_ns();
-        peers_signal_and_wait(P);
+        if (!waited) peers_signal_and_wait(P);
         if (t == 0) tp1 = globaltimer_ns();
         // all ranks' values of a batch are requested before the first is used (one NVLink round trip per batch, not one
         // per rank); the adds then run in rank order, so every rank forms bit-identical sums
@@ -154,7 +216,7 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
         }
         __syncthreads();
         code_cnt = cnt_red;
-        if (t == 0) {
+        if (t == 0 && !waited) {
             scal->wait_us += (float)(tp1 - tp0) * 1e-3f;
             scal->read_us += (float)(globaltimer_ns() - tp1) * 1e-3f;
             scal->n_steps += 1.f;
@@ -264,6 +326,8 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
                  __nv_bfloat16* __restrict__ E_bf16, float* __restrict__ e_norm2, int norm_elems, const Peers P) {
     pdl_wait();
     pdl_trigger();
+    const bool use_red = kPeer && do_ema && P.red != nullptr;
+    if (use_red) peers_wait(P, FLAG_PHASE2);      // every rank's slice of the reduced sums has landed in this rank's copy
     const int lane = threadIdx.x & 31;
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (k >= norm_elems) return;
@@ -292,7 +356,7 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
     float nrm = 0.f;
     constexpr int DB = 4;                     // elements per lane whose peer loads are in flight together
     extern __shared__ float mc_row[];         // multicast path: [8 warps][D] rank-summed rows
-    const bool use_mc = kPeer && do_ema && P.mc != nullptr;
+    const bool use_mc = kPeer && do_ema && P.mc != nullptr && !use_red;
     float* my_row = mc_row + (threadIdx.x >> 5) * D;
     if (use_mc) {
         // in-switch reduction: every lane asks for 16 bytes of the row's sum over ranks (all requests of the row are in
@@ -307,7 +371,10 @@ ema_apply_kernel(float* __restrict__ E, float* __restrict__ ema_cnt, float* __re
     }
     for (int d0 = lane; d0 < D; d0 += 32 * DB) {
         float cs[DB];
-        if (use_mc) {
+        if (use_red) {                        // written by the peers through the switch: read from L2, never a stale L1 line
+#pragma unroll
+            for (int b = 0; b < DB; ++b) cs[b] = d0 + 32 * b < D ? __ldcg(P.red + (int64_t)k * D + d0 + 32 * b) : 0.f;
+        } else if (use_mc) {
 #pragma unroll
             for (int b = 0; b < DB; ++b) cs[b] = d0 + 32 * b < D ? my_row[d0 + 32 * b] : 0.f;
         } else if (do_ema && kPeer) {         // one NVLink round trip for DB x world values, adds in rank order
@@ -391,10 +458,16 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                       int K, int D, float decay, float eps, int do_ema, int search, void* E_bf16, float* e_norm2,
                       int64_t* usage_total, int32_t* steps_since_used, float* perplexity, int32_t* n_dead,
                       int dead_after, int update_usage, void* ws, cudaStream_t st, const void* const* peer_stats,
-                      void* const* peer_flags, int world, int rank, int epoch, const void* mc_stats) {
+                      void* const* peer_flags, int world, int rank, int epoch, const void* mc_stats, void* mc_reduced,
+                      const void* reduced_local) {
     Peers P;
     P.world = 0; P.rank = 0; P.epoch = 0; P.timeout_ns = peer_timeout_ns();
     P.mc = static_cast<const float*>(mc_stats);
+    // two-phase form: needs the in-switch sum, 16-byte granules, and something to apply (st mode exchanges counts only)
+    const bool two_phase = mc_stats != nullptr && mc_reduced != nullptr && reduced_local != nullptr && do_ema &&
+                           ((int64_t)K * D) % 4 == 0 && peer_stats != nullptr;
+    P.mc_red = two_phase ? static_cast<float*>(mc_reduced) : nullptr;
+    P.red = two_phase ? static_cast<const float*>(reduced_local) : nullptr;
     const bool peer = peer_stats != nullptr;
     if (peer) {
         VQ_REQUIRE(world >= 1 && world <= VQ_MAX_PEERS && rank >= 0 && rank < world && peer_flags != nullptr && epoch > 0,
@@ -418,6 +491,14 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
         VQ_REQUIRE(!do_ema || (ema_cnt != nullptr && ema_sum != nullptr && code_sum != nullptr),
                    "vq_ema_update: do_ema needs ema_cnt, ema_sum and code_sum");
         float* cnt_red = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256);    // reserved by ws_layout
+        if (two_phase) {
+            const int64_t KD4 = (int64_t)K * D / 4, per = (KD4 + world - 1) / world;
+            int64_t blocks = (per + 1023) / 1024;
+            blocks = blocks < 1 ? 1 : (blocks > 2 * sm_count() ? 2 * sm_count() : blocks);
+            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_reduce_slice_kernel, dim3((unsigned)blocks), dim3(256), 0, st, KD4, P, scal));
+            VQ_CHECK_CUDA(cudaGetLastError());
+            count_launch();
+        }
         if (peer)
             VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<true>, dim3(1), dim3(1024), 0, st, ema_cnt, code_cnt, K, decay, do_ema,
                                      scal, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, P,
@@ -434,7 +515,7 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
     }
     const int ne = round_up(K, 256);                 // codes incl. padding; vq_norm_elems(K) floats = ne norms + aug image
     const float k_eps = (float)((double)K * (double)eps);
-    const size_t apply_smem = (peer && do_ema && P.mc != nullptr) ? (size_t)8 * D * sizeof(float) : 0;
+    const size_t apply_smem = (peer && do_ema && P.mc != nullptr && !two_phase) ? (size_t)8 * D * sizeof(float) : 0;
     VQ_REQUIRE(apply_smem <= 48 * 1024, "vq_ema_update_dp: D=%d too large for the multicast path (D <= 1536)", D);
     VQ_CHECK_CUDA(launch_pdl(PDL_APPLY, (peer && do_ema) ? ema_apply_kernel<true> : ema_apply_kernel<false>, dim3((ne + 7) / 8),
                              dim3(256), apply_smem, st, E_f32, ema_cnt, ema_sum, code_cnt, code_sum, K, D, decay, eps, k_eps, do_ema,

@@ -253,7 +253,8 @@ def ema_update_dp(E: torch.Tensor, ema_cnt: torch.Tensor, ema_sum: torch.Tensor,
                   do_ema: bool, search: str, E_bf16: Optional[torch.Tensor], e_norm2: torch.Tensor,
                   usage_total: torch.Tensor, steps_since_used: torch.Tensor, perplexity: torch.Tensor,
                   n_dead: torch.Tensor, dead_after: int, update_usage: bool, ws: torch.Tensor, peer_stats, peer_flags,
-                  rank: int, epoch: int, mc_stats: Optional[int] = None) -> None:
+                  rank: int, epoch: int, mc_stats: Optional[int] = None, mc_reduced: Optional[int] = None,
+                  reduced_local: Optional[int] = None) -> None:
     """a-6 fused into a-7..a-9: the update kernels add every rank's statistics through peer memory
     (peer_stats / peer_flags: lists of `world` raw device pointers, own buffers at index `rank`)."""
     with _On(E, ema_cnt, ema_sum, E_bf16, e_norm2, usage_total, steps_since_used, perplexity, n_dead, ws) as on:
@@ -266,4 +267,5 @@ def ema_update_dp(E: torch.Tensor, ema_cnt: torch.Tensor, ema_sum: torch.Tensor,
                                            int(bool(do_ema)), SEARCH_MODES[search] & 3, _ptr(E_bf16), _ptr(e_norm2),
                                            _ptr(usage_total), _ptr(steps_since_used), _ptr(perplexity), _ptr(n_dead),
                                            int(dead_after), int(bool(update_usage)), _ptr(ws), ps, pf, world, int(rank),
-                                           int(epoch), mc_stats or None, on.stream), "vq_ema_update_dp")
+                                           int(epoch), mc_stats or None, mc_reduced or None, reduced_local or None,
+                                           on.stream), "vq_ema_update_dp")

@@ -89,9 +89,14 @@ class SymmExchange:
     """Statistics exchange buffers on torch symmetric memory (plumbing only: allocation + rendezvous): same layout and
     interface as PeerExchange -- [stats 0 | stats 1 | flags] per rank, peer pointers for the flags -- plus, where the
     node has NVLS, the MULTICAST address of the allocation: the EMA kernels then read every statistic with one
-    multimem.ld_reduce (sum over ranks formed inside the NVSwitch, one NVLink read per element instead of W)."""
+    multimem.ld_reduce (sum over ranks formed inside the NVSwitch, one NVLink read per element instead of W).
+    reduced_numel > 0 adds a [reduced_numel] float region behind the flags for the two-phase form (include/vq_b200.h,
+    vq_ema_update_dp: mc_reduced / reduced_local), used for codebooks of TWO_PHASE_MIN_BYTES and more."""
 
-    def __init__(self, numel: int, device: torch.device, group=None, timeout_s: Optional[float] = None):
+    TWO_PHASE_MIN_BYTES = 2 << 20        # K*D*4; below it the one-phase form (one kernel, one flag round less) wins
+
+    def __init__(self, numel: int, device: torch.device, group=None, timeout_s: Optional[float] = None,
+                 reduced_numel: int = 0):
         import torch.distributed._symmetric_memory as symm
         from . import _lib
         lib = _lib.load()
@@ -104,7 +109,8 @@ class SymmExchange:
             raise RuntimeError(f"SymmExchange supports at most {_lib.MAX_PEERS} ranks")
         stats_bytes = (self.numel * 4 + 255) // 256 * 256
         self._stats_bytes = stats_bytes
-        total_f = (2 * stats_bytes + 256) // 4
+        self._red_numel = int(reduced_numel)
+        total_f = (2 * stats_bytes + 256) // 4 + self._red_numel
         g = group if group is not None else dist.group.WORLD
         self._t = symm.empty(total_f, dtype=torch.float32, device=device)
         self._h = symm.rendezvous(self._t, g.group_name)
@@ -114,7 +120,10 @@ class SymmExchange:
         self._mc_base = int(mc) if os.environ.get("VQ_PEER_MULTICAST", "1") != "0" else 0
         self.stats = [self._t[i * stats_bytes // 4: i * stats_bytes // 4 + self.numel] for i in range(2)]
         self.epoch = 0
-        self.kind = "symm+multicast" if self._mc_base else "symm"
+        tp = os.environ.get("VQ_PEER_TWO_PHASE", "auto")
+        self._two_phase = bool(self._mc_base) and self._red_numel > 0 and tp != "0" and \
+            (tp == "1" or self._red_numel * 4 >= self.TWO_PHASE_MIN_BYTES)
+        self.kind = ("symm+multicast, two-phase" if self._two_phase else "symm+multicast") if self._mc_base else "symm"
         torch.cuda.synchronize(device)
         dist.barrier(group=group)            # every allocation is zeroed and mapped before the first signal
 
@@ -131,6 +140,13 @@ class SymmExchange:
     def mc_stats(self):
         return self._mc_base + (self.epoch & 1) * self._stats_bytes if self._mc_base else None
 
+    def reduced(self):
+        """(multicast address, this rank's address) of the reduced-sums region, or (None, None): one-phase exchange."""
+        if not self._two_phase:
+            return None, None
+        off = 2 * self._stats_bytes + 256
+        return self._mc_base + off, self._t.data_ptr() + off
+
     def close(self) -> None:
         if self._t is None:
             return
@@ -140,14 +156,15 @@ class SymmExchange:
         self._t, self._h, self.stats = None, None, []
 
 
-def make_exchange(numel: int, device: torch.device, group=None, timeout_s: Optional[float] = None):
+def make_exchange(numel: int, device: torch.device, group=None, timeout_s: Optional[float] = None,
+                  reduced_numel: int = 0):
     """Symmetric-memory exchange (with the in-switch reduction where the node has NVLS) when torch provides it, else the
     CUDA-IPC one.  VQ_PEER_SYMM=0 forces the IPC path.  Every rank takes the same branch (the choice is all-reduced)."""
     ok = os.environ.get("VQ_PEER_SYMM", "1") != "0"
     ex = None
     if ok:
         try:
-            ex = SymmExchange(numel, device, group, timeout_s)
+            ex = SymmExchange(numel, device, group, timeout_s, reduced_numel)
         except Exception as exc:          # no symmetric memory on this build / node: the IPC path does the same job
             import warnings
             warnings.warn(f"vqvae_b200: symmetric-memory exchange unavailable ({type(exc).__name__}: {exc}); using CUDA IPC")
@@ -212,6 +229,9 @@ class PeerExchange:
 
     def mc_stats(self):
         return None
+
+    def reduced(self):
+        return None, None
 
     def next_buffer(self) -> torch.Tensor:
         """Statistics buffer the NEXT step writes (call once per step, before the pass kernel)."""

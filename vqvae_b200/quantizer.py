@@ -357,7 +357,8 @@ class VectorQuantizer(nn.Module):
             self.peer_exchange = "nccl"
             return False
         K, D = self.codebook_size, self.emb_dim
-        ex = parallel.make_exchange(K * D + K, self.codebook.device, self.process_group, timeout_s=self.peer_timeout_s)
+        ex = parallel.make_exchange(K * D + K, self.codebook.device, self.process_group, timeout_s=self.peer_timeout_s,
+                                    reduced_numel=K * D)
         if self.peer_exchange == "auto" and ex.mc_stats() is None \
                 and (K * (D + 1)) * 4 * world > PEER_ONE_SHOT_MAX_BYTES:
             # no in-switch reduction here, so every rank would read all W buffers (one-shot): right for small statistics
@@ -518,10 +519,11 @@ class VectorQuantizer(nn.Module):
         if ema and self._peers is not None and self._use_peers():
             E = self.codebook.detach()
             px = self._peers
+            mc_red, red = px.reduced()
             ops.ema_update_dp(E, self.ema_cnt, self.ema_sum, self.ema_decay, self.ema_eps, True, search, self._E_bf16,
                               self._e_norm2, self.usage_total, self.steps_since_used, self.last_perplexity, self.n_dead,
                               self.dead_after, True, ws, px.peer_stats(), px.peer_flags(), px.rank, px.epoch,
-                              mc_stats=px.mc_stats())
+                              mc_stats=px.mc_stats(), mc_reduced=mc_red, reduced_local=red)
             self._shadow_key = (E.data_ptr(), E._version, search)
             return
         if self._dist_active():
