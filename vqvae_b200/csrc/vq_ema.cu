@@ -222,17 +222,36 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
             scal->n_steps += 1.f;
         }
     }
-    for (int k = t; k < K; k += 1024) {
-        const float c = code_cnt[k];
-        if (do_ema) s_n += (double)__fadd_rn(__fmul_rn(decay, ema_cnt[k]), __fmul_rn(omg, c));
-        s_c += (double)c;
-        if (update_usage) {
-            usage_total[k] += (int64_t)llrintf(c);
-            const int s = c > 0.f ? 0 : steps_since_used[k] + 1;
-            steps_since_used[k] = s;
-            dead += s >= dead_after;
-        } else {
-            dead += steps_since_used[k] >= dead_after;
+    // one block walks K counters: the loads of TB codes per thread are issued together (the loop is latency-, not
+    // bandwidth-bound: 15.8 -> us at K = 8192 with one load chain per iteration); sums keep the order k = t, t+1024, ...
+    constexpr int TB = 8;
+    for (int k0 = t; k0 < K; k0 += 1024 * TB) {
+        float c[TB], e[TB];
+        int64_t u[TB];
+        int32_t ssu[TB];
+#pragma unroll
+        for (int b = 0; b < TB; ++b) {
+            const int k = k0 + 1024 * b;
+            const bool in = k < K;
+            c[b] = in ? code_cnt[k] : 0.f;
+            e[b] = (in && do_ema) ? ema_cnt[k] : 0.f;
+            u[b] = (in && update_usage) ? usage_total[k] : 0;
+            ssu[b] = in ? steps_since_used[k] : 0;
+        }
+#pragma unroll
+        for (int b = 0; b < TB; ++b) {
+            const int k = k0 + 1024 * b;
+            if (k >= K) break;
+            if (do_ema) s_n += (double)__fadd_rn(__fmul_rn(decay, e[b]), __fmul_rn(omg, c[b]));
+            s_c += (double)c[b];
+            if (update_usage) {
+                usage_total[k] = u[b] + (int64_t)llrintf(c[b]);
+                const int s = c[b] > 0.f ? 0 : ssu[b] + 1;
+                steps_since_used[k] = s;
+                dead += s >= dead_after;
+            } else {
+                dead += ssu[b] >= dead_after;
+            }
         }
     }
     double v[3] = {s_n, s_c, (double)dead};
@@ -262,9 +281,16 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
     // perplexity = exp(-sum p log(p + 1e-10))
     double h = 0.0;
     if (tot_c > 0.0)
-        for (int k = t; k < K; k += 1024) {
-            const float p = (float)((double)code_cnt[k] / tot_c);
-            h += (double)(p * logf(p + 1e-10f));
+        for (int k0 = t; k0 < K; k0 += 1024 * TB) {
+            float c[TB];
+#pragma unroll
+            for (int b = 0; b < TB; ++b) c[b] = k0 + 1024 * b < K ? code_cnt[k0 + 1024 * b] : 0.f;
+#pragma unroll
+            for (int b = 0; b < TB; ++b) {
+                if (k0 + 1024 * b >= K) break;
+                const float p = (float)((double)c[b] / tot_c);
+                h += (double)(p * logf(p + 1e-10f));
+            }
         }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
