@@ -235,7 +235,9 @@ __device__ __forceinline__ int finish_deferred(float best, int bcol, uint32_t sl
 // instruction over a 256-row slab (128 rows per CTA) x 256 codes (128 codes of each stage in each CTA's shared memory,
 // see vq_common.cuh).  Per SM that halves the codebook bytes pulled from L2 (the binding resource of the single-CTA
 // kernel: 148 SMs x 64 B/clk against an L2 that delivers about 43 B/clk/SM) and the operand bytes read from shared memory.
-template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair>
+// kPlanes (1, or 2 = split fp32 tier) is a template parameter on purpose: as a run-time loop bound in the producer and the MMA
+// issuer it cost the bf16 search 12-15 % at D = 256 (1.42 -> 1.60 ms at C4, same box, profiles/r02/search_planes_ab.log).
+template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair, int kPlanes>
 __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
                  const __grid_constant__ CUtensorMap tm_aug, const float* __restrict__ norms, int64_t N, int K, int D,
@@ -252,7 +254,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smA = smem;
-    uint8_t* smB = smA + nabuf * ok.planes * nkb * A_KB_BYTES;
+    uint8_t* smB = smA + nabuf * kPlanes * nkb * A_KB_BYTES;
     const int num_nb = (K + BN - 1) / BN;
     float* smN = reinterpret_cast<float*>(smB + nstages * B_ST);
     uint8_t* smP = reinterpret_cast<uint8_t*>(smN) + (kNormSmem ? num_nb * BN * 4 : 0);   // kMode 2: parked groups
@@ -268,7 +270,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
     const int64_t nunits = kPair ? (gridDim.x >> 1) : gridDim.x;
     constexpr int SLAB = kPair ? 2 * BM : BM;                             // rows per slab of the unit
     const int64_t ntiles = (N + SLAB - 1) / SLAB;
-    const int npl = ok.planes;                                            // 2: split fp32 tier
+    constexpr int npl = kPlanes;                                            // 2: split fp32 tier
     const int a_bytes = npl * nkb * A_KB_BYTES;
 
     if (warp == 0 && lane == 0) {
@@ -738,19 +740,31 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
                  const OperandKind, int32_t*, float*, const Presort);
 #endif
-#define VQ_PICK3(NS, EW, P)                                                                       \
-    (mode == 3 ? assign_tc_kernel<false, EW, 3, P> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P>  \
-                                                 : mode == 1 ? assign_tc_kernel<NS, EW, 1, P> : assign_tc_kernel<NS, EW, 0, P>)
+#define VQ_PICK4(NS, EW, P, PL)                                                                              \
+    (mode == 3 ? assign_tc_kernel<false, EW, 3, P, PL> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P, PL>         \
+                                                     : mode == 1 ? assign_tc_kernel<NS, EW, 1, P, PL> : assign_tc_kernel<NS, EW, 0, P, PL>)
+#define VQ_PICK3(NS, EW, P) (planes == 2 ? VQ_PICK4(NS, EW, P, 2) : VQ_PICK4(NS, EW, P, 1))
 #define VQ_PICK(NS, EW) (pair ? VQ_PICK3(NS, EW, true) : VQ_PICK3(NS, EW, false))
-#ifdef VQ_TUNING
-    if (norm_smem) kern = epi_warps == 4 ? VQ_PICK(true, 4) : epi_warps == 8 ? VQ_PICK(true, 8) : VQ_PICK(true, 16);
-    else kern = epi_warps == 4 ? VQ_PICK(false, 4) : epi_warps == 8 ? VQ_PICK(false, 8) : VQ_PICK(false, 16);
-#else       // product build: pairs run 8 epilogue warps, single CTAs 16 (14 instantiations instead of 42)
+#ifdef VQ_TUNING                // the epilogue-warp knob exists for the one-plane kernels only
+    if (planes == 2) {
+        if (norm_smem) kern = pair ? VQ_PICK4(true, 8, true, 2) : VQ_PICK4(true, 16, false, 2);
+        else kern = pair ? VQ_PICK4(false, 8, true, 2) : VQ_PICK4(false, 16, false, 2);
+    } else if (norm_smem) {
+        kern = epi_warps == 4 ? (pair ? VQ_PICK4(true, 4, true, 1) : VQ_PICK4(true, 4, false, 1))
+             : epi_warps == 8 ? (pair ? VQ_PICK4(true, 8, true, 1) : VQ_PICK4(true, 8, false, 1))
+                              : (pair ? VQ_PICK4(true, 16, true, 1) : VQ_PICK4(true, 16, false, 1));
+    } else {
+        kern = epi_warps == 4 ? (pair ? VQ_PICK4(false, 4, true, 1) : VQ_PICK4(false, 4, false, 1))
+             : epi_warps == 8 ? (pair ? VQ_PICK4(false, 8, true, 1) : VQ_PICK4(false, 8, false, 1))
+                              : (pair ? VQ_PICK4(false, 16, true, 1) : VQ_PICK4(false, 16, false, 1));
+    }
+#else       // product build: pairs run 8 epilogue warps, single CTAs 16 (28 instantiations: 14 per plane count)
     if (norm_smem) kern = pair ? VQ_PICK3(true, 8, true) : VQ_PICK3(true, 16, false);
     else kern = pair ? VQ_PICK3(false, 8, true) : VQ_PICK3(false, 16, false);
 #endif
 #undef VQ_PICK
 #undef VQ_PICK3
+#undef VQ_PICK4
     VQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
 
     cudaLaunchConfig_t cfg = {};
