@@ -237,11 +237,13 @@ __device__ __forceinline__ int finish_deferred(float best, int bcol, uint32_t sl
 // kernel: 148 SMs x 64 B/clk against an L2 that delivers about 43 B/clk/SM) and the operand bytes read from shared memory.
 // kPlanes (1, or 2 = split fp32 tier) is a template parameter on purpose: as a run-time loop bound in the producer and the MMA
 // issuer it cost the bf16 search 12-15 % at D = 256 (1.42 -> 1.60 ms at C4, same box, profiles/r02/search_planes_ab.log).
-template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair, int kPlanes>
+// kNKB: number of 64-feature K-blocks when D is 64, 128 or 256 (the shapes of BASELINE.json), 0 = read it from the argument.
+// Same reason: with the K-block loops fully unrolled the search is another 4 % faster (C4 1.33 -> 1.28 ms, C2 261 -> 250 us).
+template <bool kNormSmem, int kEpiWarps, int kMode, bool kPair, int kPlanes, int kNKB>
 __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant__ CUtensorMap tm_e,
                  const __grid_constant__ CUtensorMap tm_aug, const float* __restrict__ norms, int64_t N, int K, int D,
-                 int nkb, int nstages, int nabuf, const OperandKind ok, int32_t* __restrict__ idx, float* __restrict__ smin,
+                 int nkb_arg, int nstages, int nabuf, const OperandKind ok, int32_t* __restrict__ idx, float* __restrict__ smin,
 #ifdef VQ_TUNING
                  int dbg,               // 1..4: timing experiments of the tuning build (results are WRONG); 0 = off
 #endif
@@ -249,6 +251,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
 #ifndef VQ_TUNING
     constexpr int dbg = 0;             // the product build has no result-changing switches
 #endif
+    const int nkb = kNKB != 0 ? kNKB : nkb_arg;          // compile-time for D = 64 * kNKB
     constexpr int B_ROWS = kPair ? BN / 2 : BN;          // codes of a stage held by this CTA
     constexpr int B_ST = B_ROWS * BK * 2;                // ring slot bytes (16 KiB / 32 KiB)
     extern __shared__ uint8_t smem_raw[];
@@ -402,7 +405,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_z, const __grid_constant
                     const uint32_t d_tmem = tmem_base + acc * BN;
                     for (int kb = 0; kb < nkb; ++kb) {
                         const int rem = D - kb * BK;
-                        const int ksteps = rem >= BK ? BK / UK : (rem + UK - 1) / UK;
+                        const int ksteps = (kNKB != 0 || rem >= BK) ? BK / UK : (rem + UK - 1) / UK;
                         for (int pb = 0; pb < npl; ++pb) {
                             mbar_wait(&ctl->b_full[st], ph, 5);
                             tc_fence_after();
@@ -740,9 +743,9 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const float*, int64_t, int, int, int, int, int,
                  const OperandKind, int32_t*, float*, const Presort);
 #endif
-#define VQ_PICK4(NS, EW, P, PL)                                                                              \
-    (mode == 3 ? assign_tc_kernel<false, EW, 3, P, PL> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P, PL>         \
-                                                     : mode == 1 ? assign_tc_kernel<NS, EW, 1, P, PL> : assign_tc_kernel<NS, EW, 0, P, PL>)
+#define VQ_PICK4(NS, EW, P, PL)                                                                                  \
+    (mode == 3 ? assign_tc_kernel<false, EW, 3, P, PL, 0> : mode == 2 ? assign_tc_kernel<NS, EW, 2, P, PL, 0>       \
+                                                        : mode == 1 ? assign_tc_kernel<NS, EW, 1, P, PL, 0> : assign_tc_kernel<NS, EW, 0, P, PL, 0>)
 #define VQ_PICK3(NS, EW, P) (planes == 2 ? VQ_PICK4(NS, EW, P, 2) : VQ_PICK4(NS, EW, P, 1))
 #define VQ_PICK(NS, EW) (pair ? VQ_PICK3(NS, EW, true) : VQ_PICK3(NS, EW, false))
 #ifdef VQ_TUNING                // the epilogue-warp knob exists for the one-plane kernels only
@@ -762,6 +765,14 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     if (norm_smem) kern = pair ? VQ_PICK3(true, 8, true) : VQ_PICK3(true, 16, false);
     else kern = pair ? VQ_PICK3(false, 8, true) : VQ_PICK3(false, 16, false);
 #endif
+    // the BASELINE shapes (D = 64, 128, 256 on CTA pairs, one plane, the epilogue mode the shape picks by itself) run the
+    // instantiations with a compile-time K-block count
+    if (pair && planes == 1 && epi_warps == 8 && D % BK == 0) {
+        if (D == 64 && mode == 3) kern = assign_tc_kernel<false, 8, 3, true, 1, 1>;
+        else if (D == 128 && mode == 3) kern = assign_tc_kernel<false, 8, 3, true, 1, 2>;
+        else if (D == 256 && mode == 1) kern = norm_smem ? assign_tc_kernel<true, 8, 1, true, 1, 4> : assign_tc_kernel<false, 8, 1, true, 1, 4>;
+        else if (D == 256 && mode == 2) kern = norm_smem ? assign_tc_kernel<true, 8, 2, true, 1, 4> : assign_tc_kernel<false, 8, 2, true, 1, 4>;
+    }
 #undef VQ_PICK
 #undef VQ_PICK3
 #undef VQ_PICK4
