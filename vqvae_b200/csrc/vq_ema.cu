@@ -113,68 +113,38 @@ __device__ __forceinline__ void peers_signal_and_wait(const Peers& P) {
     peers_wait(P);
 }
 
-// Two-phase exchange for large codebooks (reduce-scatter -> all-gather inside the switch).  With one-phase reads every
-// rank pulls the whole [K*D] sum through the switch, so each GPU's NVLink carries W x K*D x 4 bytes outbound per step
-// (measured: ema_apply_kernel<true> 35 us at 2 GPUs, 55 us at 4, K=8192 D=256).  Here rank r reduces only the r-th 1/W of
-// the flat [K*D] array (multimem.ld_reduce: summed in the switch) and writes the result to EVERY rank's "reduced" region
-// with one multimem.st per 16 bytes (replicated by the switch): K*D x 4 bytes out and in per GPU whatever W is.  Every
-// rank then applies the EMA step from its own copy, which holds the same bits on all ranks.
-// First kernel of the update: block 0 signals phase 1, all blocks wait for it (polling this rank's own flag array), the
-// last block to finish signals phase 2.  ema_totals_kernel runs between this kernel and ema_apply_kernel, which hides the
-// phase-2 flag's flight time.
-__global__ void __launch_bounds__(256)
-ema_reduce_slice_kernel(int64_t KD4, const Peers P, Scal* __restrict__ scal) {
-    __shared__ int s_last;
-    pdl_wait();
-    pdl_trigger();
-    const int t = threadIdx.x;
-    unsigned long long tp0 = 0, tp1 = 0;
-    if (blockIdx.x == 0) {
-        if (t == 0) tp0 = globaltimer_ns();
-        peers_signal(P);
-    }
-    peers_wait(P);
-    if (blockIdx.x == 0 && t == 0) tp1 = globaltimer_ns();
-    const int64_t per = (KD4 + P.world - 1) / P.world;
-    const int64_t i0 = per * P.rank, i1 = i0 + per < KD4 ? i0 + per : KD4;
-    constexpr int U = 4;                                  // 16-byte requests in flight per thread
-    for (int64_t b = i0 + ((int64_t)blockIdx.x * U) * 256 + t; b < i1; b += (int64_t)gridDim.x * U * 256) {
-        float4 v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-            if (b + u * 256 < i1) v[u] = ld_reduce_v4(P.mc + 4 * (b + u * 256));
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-            if (b + u * 256 < i1) st_multicast_v4(P.mc_red + 4 * (b + u * 256), v[u]);
-    }
-    __threadfence_system();
-    __syncthreads();
-    int32_t* ctr = P.flags[P.rank] + FLAG_COUNTER;
-    if (t == 0) s_last = atomicAdd(ctr, 1) == (int)gridDim.x - 1;
-    __syncthreads();
-    if (s_last) {
-        peers_signal(P, FLAG_PHASE2);
-        if (t == 0) *ctr = 0;
-    }
-    if (blockIdx.x == 0 && t == 0) {
-        scal->wait_us += (float)(tp1 - tp0) * 1e-3f;
-        scal->read_us += (float)(globaltimer_ns() - tp1) * 1e-3f;
-        scal->n_steps += 1.f;
-    }
-}
-
 // one block.  tot_new = sum_k (g n_k + (1-g) cnt_k) in a fixed order (double); usage / dead / perplexity.
 // kPeer: code_cnt is the sum over ranks of the peers' counts (read over NVLink after the flag exchange); the reduced
 // counts are also written to cnt_red (local) for the second pass below and for ema_apply_kernel.
+struct TotalsArgs {
+    const float* ema_cnt;
+    const float* code_cnt;
+    int K;
+    float decay;
+    int do_ema;
+    Scal* scal;
+    int64_t* usage_total;
+    int32_t* steps_since_used;
+    float* perplexity;
+    int32_t* n_dead;
+    int dead_after, update_usage;
+    int64_t KD;
+    float* cnt_red;
+};
+// body of the totals step for ONE block of 1024 threads (sh: 3 x 32 doubles of shared memory)
 template <bool kPeer>
-__global__ void __launch_bounds__(1024)
-ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ code_cnt, int K, float decay,
-                  int do_ema, Scal* __restrict__ scal, int64_t* __restrict__ usage_total,
-                  int32_t* __restrict__ steps_since_used, float* __restrict__ perplexity, int32_t* __restrict__ n_dead,
-                  int dead_after, int update_usage, const Peers P, int64_t KD, float* __restrict__ cnt_red) {
-    __shared__ double sh[3][32];
-    pdl_wait();
-    pdl_trigger();
+__device__ __forceinline__ void totals_body(const TotalsArgs& A, const Peers& P, double (*sh)[32]) {
+    const float* __restrict__ ema_cnt = A.ema_cnt;
+    const float* __restrict__ code_cnt = A.code_cnt;
+    const int K = A.K, do_ema = A.do_ema, dead_after = A.dead_after, update_usage = A.update_usage;
+    const float decay = A.decay;
+    Scal* __restrict__ scal = A.scal;
+    int64_t* __restrict__ usage_total = A.usage_total;
+    int32_t* __restrict__ steps_since_used = A.steps_since_used;
+    float* __restrict__ perplexity = A.perplexity;
+    int32_t* __restrict__ n_dead = A.n_dead;
+    const int64_t KD = A.KD;
+    float* __restrict__ cnt_red = A.cnt_red;
     const int t = threadIdx.x;
     const float omg = 1.0f - decay;
     double s_n = 0.0, s_c = 0.0;
@@ -301,6 +271,71 @@ ema_totals_kernel(const float* __restrict__ ema_cnt, const float* __restrict__ c
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
         if (t == 0) perplexity[0] = tot_c > 0.0 ? (float)exp(-h) : 1.0f;
+    }
+}
+
+template <bool kPeer>
+__global__ void __launch_bounds__(1024) ema_totals_kernel(const TotalsArgs A, const Peers P) {
+    __shared__ double sh[3][32];
+    pdl_wait();
+    pdl_trigger();
+    totals_body<kPeer>(A, P, sh);
+}
+
+// Two-phase exchange for large codebooks (reduce-scatter -> all-gather inside the switch).  With one-phase reads every
+// rank pulls the whole [K*D] sum through the switch, so each GPU's NVLink carries W x K*D x 4 bytes outbound per step
+// (measured: ema_apply_kernel<true> 35 us at 2 GPUs, 55 us at 4, K=8192 D=256).  Here rank r reduces only the r-th 1/W of
+// the flat [K*D] array (multimem.ld_reduce: summed in the switch) and writes the result to EVERY rank's "reduced" region
+// with one multimem.st per 16 bytes (replicated by the switch): K*D x 4 bytes out and in per GPU whatever W is.  Every
+// rank then applies the EMA step from its own copy, which holds the same bits on all ranks.
+// First kernel of the update, blocks of 1024 threads: block 0 signals phase 1, all blocks wait for it (polling this
+// rank's own flag array); blocks 0 .. gridDim.x-2 move the slice and the last of them to finish signals phase 2; the
+// LAST block does the totals step (counts summed in the switch, n totals, usage, dead codes, perplexity) at the same
+// time, so the K-length reductions cost no time of their own and the phase-2 flags fly while they run.
+__global__ void __launch_bounds__(1024)
+ema_reduce_totals_kernel(int64_t KD4, const TotalsArgs A, const Peers P) {
+    __shared__ double sh[3][32];
+    __shared__ int s_last;
+    pdl_wait();
+    pdl_trigger();
+    const int t = threadIdx.x;
+    const int nslice = (int)gridDim.x - 1;                // blocks that move the slice
+    unsigned long long tp0 = 0, tp1 = 0;
+    if (blockIdx.x == 0) {
+        if (t == 0) tp0 = globaltimer_ns();
+        peers_signal(P);
+    }
+    peers_wait(P);
+    if ((int)blockIdx.x == nslice) {                      // totals block (P.red != NULL: it does not wait again)
+        totals_body<true>(A, P, sh);
+        return;
+    }
+    if (blockIdx.x == 0 && t == 0) tp1 = globaltimer_ns();
+    const int64_t per = (KD4 + P.world - 1) / P.world;
+    const int64_t i0 = per * P.rank, i1 = i0 + per < KD4 ? i0 + per : KD4;
+    constexpr int U = 4;                                  // 16-byte requests in flight per thread
+    for (int64_t b = i0 + ((int64_t)blockIdx.x * U) * 1024 + t; b < i1; b += (int64_t)nslice * U * 1024) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (b + u * 1024 < i1) v[u] = ld_reduce_v4(P.mc + 4 * (b + u * 1024));
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (b + u * 1024 < i1) st_multicast_v4(P.mc_red + 4 * (b + u * 1024), v[u]);
+    }
+    __threadfence_system();
+    __syncthreads();
+    int32_t* ctr = P.flags[P.rank] + FLAG_COUNTER;
+    if (t == 0) s_last = atomicAdd(ctr, 1) == nslice - 1;
+    __syncthreads();
+    if (s_last) {
+        peers_signal(P, FLAG_PHASE2);
+        if (t == 0) *ctr = 0;
+    }
+    if (blockIdx.x == 0 && t == 0) {
+        A.scal->wait_us += (float)(tp1 - tp0) * 1e-3f;
+        A.scal->read_us += (float)(globaltimer_ns() - tp1) * 1e-3f;
+        A.scal->n_steps += 1.f;
     }
 }
 
@@ -517,22 +552,18 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
         VQ_REQUIRE(!do_ema || (ema_cnt != nullptr && ema_sum != nullptr && code_sum != nullptr),
                    "vq_ema_update: do_ema needs ema_cnt, ema_sum and code_sum");
         float* cnt_red = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256);    // reserved by ws_layout
+        TotalsArgs TA{ema_cnt, code_cnt, K, decay, do_ema, scal, usage_total, steps_since_used, perplexity, n_dead, dead_after,
+                      update_usage, peer ? (int64_t)K * D : (int64_t)0, peer ? cnt_red : nullptr};
         if (two_phase) {
             const int64_t KD4 = (int64_t)K * D / 4, per = (KD4 + world - 1) / world;
-            int64_t blocks = (per + 1023) / 1024;
-            blocks = blocks < 1 ? 1 : (blocks > 2 * sm_count() ? 2 * sm_count() : blocks);
-            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_reduce_slice_kernel, dim3((unsigned)blocks), dim3(256), 0, st, KD4, P, scal));
-            VQ_CHECK_CUDA(cudaGetLastError());
-            count_launch();
+            int64_t blocks = (per + 4095) / 4096;                       // 4 x 16 bytes per thread per round
+            blocks = blocks < 1 ? 1 : (blocks > sm_count() ? sm_count() : blocks);
+            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_reduce_totals_kernel, dim3((unsigned)blocks + 1), dim3(1024), 0, st, KD4, TA, P));
+        } else if (peer) {
+            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<true>, dim3(1), dim3(1024), 0, st, TA, P));
+        } else {
+            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<false>, dim3(1), dim3(1024), 0, st, TA, P));
         }
-        if (peer)
-            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<true>, dim3(1), dim3(1024), 0, st, ema_cnt, code_cnt, K, decay, do_ema,
-                                     scal, usage_total, steps_since_used, perplexity, n_dead, dead_after, update_usage, P,
-                                     (int64_t)K * D, cnt_red));
-        else
-            VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<false>, dim3(1), dim3(1024), 0, st, ema_cnt, code_cnt, K, decay,
-                                     do_ema, scal, usage_total, steps_since_used, perplexity, n_dead, dead_after,
-                                     update_usage, P, (int64_t)0, (float*)nullptr));
         if (peer) code_cnt = cnt_red;
         VQ_CHECK_CUDA(cudaGetLastError());
         count_launch();
