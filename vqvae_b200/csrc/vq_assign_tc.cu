@@ -676,7 +676,10 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
     if (pair_override == 1) pair = true;
   for (int attempt = 0; attempt < 2; ++attempt) {    // second round only if the pair launch turned out to be impossible
     // epilogue warps (measured on B200): pairs 8 (C4 1409 us / C2 277 us; 16: 1427 / 292; 4: 1471 / 323), single CTA 16
-    const int epi_warps = env_epi != 0 ? env_epi : (pair ? 8 : 16);
+    // ... except the D = 256, K >= 4096 shape (epilogue mode 1) on the final kernel: 16 warps 1284 us vs 1320 us at C4
+    // (profiles/r02/search_split2.log); at D = 128 both read 258 us
+    const bool wide_epi = pair && planes == 1 && D == 256 && K >= 4096 && mode_override < 0;
+    const int epi_warps = env_epi != 0 ? env_epi : (pair ? (wide_epi ? 16 : 8) : 16);
     // Epilogue mode (see fold_chunk / fold_chunk_aug).  The epilogue, not the tensor pipe, bounds this kernel when
     // D is small (a 128 x 256 tile costs D/16 MMAs but always 32768 compare-selects), so:
     //   D <= 128          mode 3: ||e||^2 rides through the tensor core as one more K step, arg-max of the raw accumulator,
@@ -767,12 +770,23 @@ int launch_assign_tc(const void* z_bf16, int64_t N, int D, int64_t ldz, const vo
 #endif
     // the BASELINE shapes (D = 64, 128, 256 on CTA pairs, one plane, the epilogue mode the shape picks by itself) run the
     // instantiations with a compile-time K-block count
-    if (pair && planes == 1 && epi_warps == 8 && D % BK == 0) {
+    if (wide_epi && epi_warps == 16) {
+        VQ_REQUIRE(mode == 1, "vq_assign(tensor core): internal: epilogue mode %d with the 16-warp plan", mode);
+        kern = norm_smem ? assign_tc_kernel<true, 16, 1, true, 1, 4> : assign_tc_kernel<false, 16, 1, true, 1, 4>;
+    } else if (pair && planes == 1 && epi_warps == 8 && D % BK == 0) {
         if (D == 64 && mode == 3) kern = assign_tc_kernel<false, 8, 3, true, 1, 1>;
         else if (D == 128 && mode == 3) kern = assign_tc_kernel<false, 8, 3, true, 1, 2>;
         else if (D == 256 && mode == 1) kern = norm_smem ? assign_tc_kernel<true, 8, 1, true, 1, 4> : assign_tc_kernel<false, 8, 1, true, 1, 4>;
         else if (D == 256 && mode == 2) kern = norm_smem ? assign_tc_kernel<true, 8, 2, true, 1, 4> : assign_tc_kernel<false, 8, 2, true, 1, 4>;
     }
+#ifdef VQ_TUNING     // the epilogue-warp knob on the specialised kernels too (4 / 16 warps), so that it compares like with like
+    if (pair && planes == 1 && epi_warps != 8 && D % BK == 0) {
+        if (D == 128 && mode == 3)
+            kern = epi_warps == 4 ? assign_tc_kernel<false, 4, 3, true, 1, 2> : assign_tc_kernel<false, 16, 3, true, 1, 2>;
+        else if (D == 256 && mode == 1 && norm_smem)
+            kern = epi_warps == 4 ? assign_tc_kernel<true, 4, 1, true, 1, 4> : assign_tc_kernel<true, 16, 1, true, 1, 4>;
+    }
+#endif
 #undef VQ_PICK
 #undef VQ_PICK3
 #undef VQ_PICK4
