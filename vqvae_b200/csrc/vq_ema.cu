@@ -313,7 +313,9 @@ ema_reduce_totals_kernel(int64_t KD4, const TotalsArgs A, const Peers P) {
     if (blockIdx.x == 0 && t == 0) tp1 = globaltimer_ns();
     const int64_t per = (KD4 + P.world - 1) / P.world;
     const int64_t i0 = per * P.rank, i1 = i0 + per < KD4 ? i0 + per : KD4;
-    constexpr int U = 4;                                  // 16-byte requests in flight per thread
+    // one 16-byte request per thread per round, spread over as many SMs as the slice has 16 KiB pieces: 16 blocks x 4
+    // requests per thread moved the 1 MiB slice of an 8-GPU step in 43 us, 64 blocks x 256 threads x 4 in 26 us
+    constexpr int U = 1;
     for (int64_t b = i0 + ((int64_t)blockIdx.x * U) * 1024 + t; b < i1; b += (int64_t)nslice * U * 1024) {
         float4 v[U];
 #pragma unroll
@@ -556,8 +558,8 @@ int launch_ema_update(float* E_f32, float* ema_cnt, float* ema_sum, const float*
                       update_usage, peer ? (int64_t)K * D : (int64_t)0, peer ? cnt_red : nullptr};
         if (two_phase) {
             const int64_t KD4 = (int64_t)K * D / 4, per = (KD4 + world - 1) / world;
-            int64_t blocks = (per + 4095) / 4096;                       // 4 x 16 bytes per thread per round
-            blocks = blocks < 1 ? 1 : (blocks > sm_count() ? sm_count() : blocks);
+            int64_t blocks = (per + 1023) / 1024;                       // 16 bytes per thread per round
+            blocks = blocks < 1 ? 1 : (blocks > sm_count() - 1 ? sm_count() - 1 : blocks);
             VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_reduce_totals_kernel, dim3((unsigned)blocks + 1), dim3(1024), 0, st, KD4, TA, P));
         } else if (peer) {
             VQ_CHECK_CUDA(launch_pdl(PDL_TOTALS, ema_totals_kernel<true>, dim3(1), dim3(1024), 0, st, TA, P));
