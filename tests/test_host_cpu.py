@@ -30,6 +30,27 @@ def test_library_exports_every_declared_symbol():
     assert lib.vq_abi_version() == _lib.ABI_VERSION == 5
 
 
+def _header_prototypes():
+    """name -> number of parameters of every function include/vq_b200.h declares (comments stripped)."""
+    src = open(os.path.join(ROOT, "include", "vq_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    out = {}
+    for m in re.finditer(r"\b(vq_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
+        args = m.group(2).strip()
+        out[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    return out
+
+
+def test_ctypes_signatures_have_the_header_arity():
+    """A prototype that gains or loses a parameter must change the binding too (ABI drift shows up here, not as a
+    mis-aligned argument on the GPU)."""
+    from vqvae_b200 import _lib
+    protos = _header_prototypes()
+    assert set(protos) == set(_lib.SIGNATURES)
+    for name, (_, argtypes) in _lib.SIGNATURES.items():
+        assert len(argtypes) == protos[name], f"{name}: header has {protos[name]} parameters, ctypes binding {len(argtypes)}"
+
+
 def test_host_only_entry_points():
     from vqvae_b200 import _lib
     lib = _lib.load(build_if_missing=True)
