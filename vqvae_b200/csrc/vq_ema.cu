@@ -37,7 +37,7 @@ struct Peers {
 };
 // flag array of a rank (int32, zero-initialised by the caller): [0, MAX_PEERS) phase 1 "statistics of epoch e complete",
 // [MAX_PEERS, 2 MAX_PEERS) phase 2 "my slice of the reduced sums of epoch e is written everywhere", [2 MAX_PEERS] block
-// counter of ema_reduce_slice_kernel (returns to 0 at the end of every launch)
+// counter of ema_reduce_totals_kernel (returns to 0 at the end of every launch)
 constexpr int FLAG_PHASE2 = VQ_MAX_PEERS, FLAG_COUNTER = 2 * VQ_MAX_PEERS;
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
@@ -151,7 +151,7 @@ __device__ __forceinline__ void totals_body(const TotalsArgs& A, const Peers& P,
     int dead = 0;
     unsigned long long tp0 = 0, tp1 = 0;
     if (kPeer) {
-        const bool waited = P.red != nullptr;     // two-phase: ema_reduce_slice_kernel (earlier in the stream) did phase 1
+        const bool waited = P.red != nullptr;     // two-phase: this block of ema_reduce_totals_kernel has already waited for phase 1
         if (t == 0) tp0 = globaltimer_ns();
         if (!waited) peers_signal_and_wait(P);
         if (t == 0) tp1 = globaltimer_ns();
