@@ -51,6 +51,29 @@ def test_ctypes_signatures_have_the_header_arity():
         assert len(argtypes) == protos[name], f"{name}: header has {protos[name]} parameters, ctypes binding {len(argtypes)}"
 
 
+def test_c_host_example_compiles_and_links(tmp_path):
+    """examples/host_c_example.c drives one step through the C ABI from plain C99: the header must be valid C and every
+    entry point it uses must resolve against the built library (running it needs a GPU)."""
+    import shutil
+    import subprocess
+    from vqvae_b200 import _lib
+    _lib.load(build_if_missing=True)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    if shutil.which("gcc") is None or not os.path.exists(os.path.join(cuda, "include", "cuda_runtime_api.h")):
+        pytest.skip("gcc or the CUDA runtime headers are not here")
+    hdr = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
+                          os.path.join(ROOT, "include", "vq_b200.h")], capture_output=True, text=True)
+    assert hdr.returncode == 0, hdr.stderr
+    exe = str(tmp_path / "host_c_example")
+    cmd = ["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-O1", os.path.join(ROOT, "examples", "host_c_example.c"),
+           "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(cuda, "include"),
+           "-L" + os.path.join(ROOT, "vqvae_b200"), "-lvq_b200", "-L" + os.path.join(cuda, "lib64"), "-lcudart", "-lm",
+           "-Wl,-rpath," + os.path.join(ROOT, "vqvae_b200"), "-o", exe]
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert os.path.exists(exe)
+
+
 def test_host_only_entry_points():
     from vqvae_b200 import _lib
     lib = _lib.load(build_if_missing=True)
