@@ -412,8 +412,6 @@ class VectorQuantizer(nn.Module):
         # the search leaves the counting-sort inputs of idx in ws, the pass picks them up (one scatter launch instead of
         # memset + histogram + scan/scatter)
         kind = VQ_STAT_SUM_RESID if self.quantizer == "st" else VQ_STAT_SUM_Z
-        # the search leaves the counting-sort inputs of idx in ws, the pass picks them up (one scatter launch instead of
-        # memset + histogram + scan/scatter)
         ops.assign(z2, E, self._E_bf16, self._e_norm2, search, idx32, None, ws, presort=True, ws_clean=True)
         ops.gather_st_loss_scatter(z2, idx32, E, q, sqerr, code_cnt, code_sum, kind, self.deterministic, ws,
                                    idx64_out=idx64, loss_out=loss, loss_scale=self._loss_scale(N), presorted=True)
