@@ -25,7 +25,6 @@ Choices that no reference line pins are marked (CHOICE) below and listed in DESI
 """
 from __future__ import annotations
 
-import math
 from dataclasses import dataclass
 from typing import Optional, Tuple
 

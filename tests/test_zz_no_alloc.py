@@ -3,8 +3,6 @@ array inside the library -- no workspace from the caller, no allocation in the c
 existing entry point (vq_gather_st_loss_scatter with a caller workspace) on two calls in a row, with the tolerances the
 other pass tests use (tests/gpu_util.py): indices and quantised rows bit-equal, counts exact, sums / loss 1e-5.
 This file is named so that pytest collects it last."""
-import ctypes as C
-
 import pytest
 import torch
 
