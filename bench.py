@@ -414,7 +414,11 @@ def measure(ctx, key, args, steps, warmup, full=True, clocks=True):
                            "frac": tf / peaks["tf_burst"], "frac_of_sustained_peak": tf / peaks["tf_sust"],
                            "traffic": load_traffic(key, "assign_tc_kernel"), "traffic_source": TRAFFIC_SOURCE,
                            "algorithmic_bytes": N * (D * 2 + 4) + K * D * 2 + K * 4,
-                           "peak_source": peaks["src"] + " burst (kernel timed alone)", "ms_per_launch": t_assign}
+                           "peak_source": peaks["src"] + " burst (kernel timed alone)", "ms_per_launch": t_assign,
+                           "frac_of_nominal_dense_bf16": tf / 2250.0,
+                           "peak_note": "peak = the pool's measured torch.matmul bf16 throughput (MEASURED_PEAKS.json), not a "
+                                        "hardware limit: a CTA-pair tcgen05 kernel that keeps its operands in shared memory "
+                                        "can exceed it (frac > 1), the nominal dense bf16 figure is 2250 TFLOP/s"}
         rec["roofline_pass"] = {"kernel": "scatter_ranked_kernel + pass_kernel (a-2..a-5; histogram / ranks / scan come "
                                           "from the search kernel; the scatter also widens the indices to int64)", "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"],
                                 "unit": "GB/s", "frac": gbs / peaks["hbm"], "traffic": load_traffic(key, "pass_group"),
